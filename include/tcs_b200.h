@@ -1,0 +1,177 @@
+/* include/tcs_b200.h - C ABI of libtcs_b200.so: the B200 (sm_100a) implementation of the random-walker
+ * point-cloud segmentation hot path of taketwo/tcs.
+ *
+ * The reference has no FFI layer: its boundary is the C++ template API compiled into
+ * librandom_walker_segmentation (src/random_walker_segmentation.cpp:44).  This header is the thin C layer
+ * underneath our C++ classes of the same names (include/tcs/ *.h); each entry point cites the reference
+ * function it replaces (file:line into taketwo/tcs @16cc7ab8).
+ *
+ * Conventions
+ *  - every function returns int: TCS_OK (0) or a negative tcs_status; nothing throws across the ABI;
+ *    tcs_last_error(ctx) gives the message of the last failure on that context.
+ *  - the caller owns host buffers; the context owns all device memory.  Pointers named d_* are DEVICE
+ *    pointers, all others are HOST pointers.  NULL output pointers mean "not wanted".
+ *  - one context = one device + one CUDA stream; it is single-threaded.  Different contexts (one or more
+ *    per GPU) may be used from different host threads concurrently.
+ *  - all work is enqueued on the context's stream; functions that return host data synchronise it.
+ *  - there is NO CPU fallback: without a CUDA device tcs_ctx_create fails with TCS_ERR_CUDA.
+ */
+#ifndef TCS_B200_H
+#define TCS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct tcs_ctx tcs_ctx;
+typedef struct tcs_graph tcs_graph;
+
+typedef enum tcs_status {
+  TCS_OK = 0,
+  TCS_ERR_CUDA = -1,       /* a CUDA runtime call failed / no device */
+  TCS_ERR_INPUT = -2,      /* invalid argument (reference: ComputeFailedException, impl/random_walker_segmentation.hpp:111) */
+  TCS_ERR_DEPTH = -3,      /* octree deeper than 21 levels (63-bit Morton key) */
+  TCS_ERR_NOT_CONVERGED = -4, /* PCG hit max_iterations (reference: "Random walker segmentation failed", :194) */
+  TCS_ERR_STATE = -5       /* call order violated (e.g. no cloud uploaded) */
+} tcs_status;
+
+/* edge-weight terms: include/graph/edge_weight_computer_terms.h:55-140 */
+enum { TCS_TERM_XYZ = 0, TCS_TERM_NORMAL = 1, TCS_TERM_CURVATURE = 2, TCS_TERM_RGB = 3 };
+/* EdgeWeightComputer::NormalizationType, include/graph/edge_weight_computer.h:210-218 */
+enum { TCS_NORM_NONE = 0, TCS_NORM_GLOBAL = 1, TCS_NORM_LOCAL = 2 };
+/* EdgeWeightComputer::SmallWeightPolicy, include/graph/edge_weight_computer.h:222-235 */
+enum { TCS_SMALL_IGNORE = 0, TCS_SMALL_COERCE = 1, TCS_SMALL_REMOVE = 2 };
+/* arithmetic mode of the order-sensitive float32 reductions (normal moments, global normaliser):
+ *   PARITY: the reference's sequential float32 order (one thread walks the list) - bit-exact with the reference order
+ *   FAST  : float32 products, sums accumulated in float64 in parallel and rounded once to float32 */
+enum { TCS_MODE_PARITY = 0, TCS_MODE_FAST = 1 };
+/* weight presets */
+enum { TCS_PRESET_CLASS = 0, /* RandomWalkerSegmentation::preComputeGraph, impl/random_walker_segmentation.hpp:120-131 */
+       TCS_PRESET_CLI = 1    /* app pipeline, src/random_walker_segmentation_app.cpp:129-134 + factory defaults */ };
+
+/* EdgeWeightComputer::addTerm<TermT>(influence, convex_influence_multiplier, normalization),
+ * include/graph/edge_weight_computer.h:259-283 */
+typedef struct tcs_term {
+  int kind;           /* TCS_TERM_* */
+  float influence;    /* sigma */
+  float convex_mult;  /* convex influence multiplier */
+  int normalization;  /* TCS_NORM_* */
+} tcs_term;
+
+typedef struct tcs_solver_opts {
+  double tolerance;      /* relative residual ||b - Lx|| / ||b|| per label column; default 1e-6 */
+  int max_iterations;    /* default 200000 */
+  int check_every;       /* iterations between float64 true-residual replacements / convergence checks; default 50 */
+  int store_potentials;  /* keep the dense V x K potentials on the device (getPotentials) */
+  int time_spmm;         /* bracket sampled SpMM launches with CUDA events (fills tcs_solve_info.spmm_ms) */
+} tcs_solver_opts;
+
+#define TCS_MAX_LABELS 64
+
+typedef struct tcs_solve_info {
+  int iterations;               /* PCG iterations executed */
+  int converged;                /* 1 if every column reached the tolerance */
+  int rows;                     /* n: unknowns (unlabelled vertices with non-zero degree) */
+  long long nnz;                /* off-diagonal entries of L (both triangles) + n diagonal entries */
+  int ncolours;                 /* K */
+  int ncomponents;
+  long long near_ties;          /* vertices whose two largest potentials differ by < 1e-6 */
+  double rel_residual[TCS_MAX_LABELS]; /* float64 true residual per colour column */
+  float spmm_ms;                /* device time summed over all SpMM launches (CUDA events, ctx stream) */
+  int spmm_launches;
+  float solve_ms;               /* device time of the whole PCG loop */
+  float stage_ms[12];           /* build, normals, smoothen, normals2, signs, weights, components, seeds,
+                                   assemble, solve, argmax, point labels (device time, CUDA events) */
+} tcs_solve_info;
+
+/* ---- context ------------------------------------------------------------------------------------------- */
+int tcs_ctx_create(int device, tcs_ctx** out);
+/* use an existing CUDA stream (cudaStream_t passed as void*), e.g. the caller's current stream */
+int tcs_ctx_create_on_stream(int device, void* cuda_stream, tcs_ctx** out);
+void tcs_ctx_destroy(tcs_ctx* ctx);
+const char* tcs_last_error(const tcs_ctx* ctx);
+int tcs_ctx_synchronize(tcs_ctx* ctx);
+void* tcs_ctx_stream(tcs_ctx* ctx);
+/* number of kernels launched by this library on this context since creation (bench.py's gpu_launches) */
+long long tcs_ctx_launch_count(const tcs_ctx* ctx);
+const char* tcs_version(void);
+
+/* ---- input cloud: RandomWalkerSegmentation::setInputCloud (random_walker_segmentation.h:170) ------------ */
+/* xyz: 3 floats per point, consecutive points xyz_stride bytes apart (12 for packed, 32 for pcl::PointXYZRGB);
+ * rgba: one uint32 per point rgba_stride bytes apart, or NULL for uncoloured clouds (pcl::PointXYZ). */
+int tcs_cloud_upload(tcs_ctx* ctx, const float* xyz, size_t xyz_stride, const uint32_t* rgba, size_t rgba_stride,
+                     size_t n);
+/* cloud already resident on the device as n records {x, y, z, rgba-bits} of 16 bytes; borrowed, not copied */
+int tcs_cloud_set_device(tcs_ctx* ctx, const void* d_xyzc, size_t n, int has_color);
+
+/* ---- graph construction -------------------------------------------------------------------------------- */
+/* VoxelGridGraphBuilder::compute, graph/impl/voxel_grid_graph_builder.hpp:69-143.
+ * leaf_order_desc: 1 = PCL <= 1.8 leaf-iterator order (the reference's), 0 = ascending Morton order. */
+int tcs_build_voxel_graph(tcs_ctx* ctx, float resolution, int leaf_order_desc, tcs_graph** out);
+/* RandomWalkerSegmentation::setInputGraph (random_walker_segmentation.h:175): user graph, edges in insertion
+ * order; rgba / normals4 / curvature / weight may be NULL. */
+int tcs_graph_create(tcs_ctx* ctx, size_t V, const float* xyz, const uint32_t* rgba, const float* normals4,
+                     const float* curvature, size_t E, const uint32_t* src, const uint32_t* tgt,
+                     const float* weight, tcs_graph** out);
+void tcs_graph_destroy(tcs_graph* g);
+int tcs_graph_sizes(const tcs_graph* g, size_t* V, size_t* E, size_t* N, int* depth);
+int tcs_graph_bbox_min(const tcs_graph* g, double* min3);
+int tcs_graph_download_vertices(tcs_graph* g, float* xyz, uint32_t* rgba, float* normals4, float* curvature);
+int tcs_graph_download_keys(tcs_graph* g, uint32_t* keys3);
+int tcs_graph_download_edges(tcs_graph* g, uint32_t* src, uint32_t* tgt, float* weight);
+int tcs_graph_download_csr(tcs_graph* g, uint32_t* rowptr, uint32_t* col, uint32_t* eid);
+/* GraphBuilder::getPointToVertexMap (graph/graph_builder.h:96-102); nil = 0xFFFFFFFF */
+int tcs_graph_download_point_to_vertex(tcs_graph* g, uint32_t* map);
+int tcs_graph_upload_xyz(tcs_graph* g, const float* xyz);
+int tcs_graph_upload_normals(tcs_graph* g, const float* normals4, const float* curvature);
+int tcs_graph_upload_weights(tcs_graph* g, const float* weight);
+
+/* ---- per-vertex / per-edge features ---------------------------------------------------------------------- */
+/* computeNormalsAndCurvatures(g, neighborhood_1ring), graph/impl/common.hpp:53-103 */
+int tcs_normals(tcs_graph* g, int one_ring, int mode);
+/* smoothen(g, spatial_sigma, influence_sigma), graph/impl/common.hpp:241-279 */
+int tcs_smoothen(tcs_graph* g, float spatial_sigma, float influence_sigma);
+/* computeSignedCurvatures(g), graph/impl/common.hpp:105-132 */
+int tcs_signed_curvatures(tcs_graph* g);
+/* EdgeWeightComputer::compute, graph/impl/edge_weight_computer.hpp:110-188 */
+int tcs_edge_weights(tcs_graph* g, const tcs_term* terms, int nterms, float threshold, int policy, int mode);
+/* createSubgraphsFromConnectedComponents, graph/impl/common.hpp:134-149: component id per vertex, ids in
+ * order of the smallest member vertex.  component (host, V ints) may be NULL. */
+int tcs_components(tcs_graph* g, int* ncomponents, int32_t* component);
+
+/* ---- random walker ------------------------------------------------------------------------------------------ */
+void tcs_solver_opts_default(tcs_solver_opts* o);
+/* seed -> nearest vertex (pcl::getApproximateIndices, impl/random_walker_segmentation.hpp:149-152) */
+int tcs_nearest_vertices(tcs_graph* g, const float* seed_xyz, size_t ns, int32_t* out);
+/* randomWalker(graph, weights, colours[, potentials, colour->column]) (random_walker.h:95-137,
+ * impl/random_walker.hpp:95-243) on all connected components at once.
+ * colours: V uint32; in: seed colours 1..ncolours (0 = unlabelled); out: labels.
+ * potentials: V x ncolours floats, column-major (column = colour - 1), or NULL. */
+int tcs_random_walker(tcs_graph* g, uint32_t* colours, int ncolours, const tcs_solver_opts* opts,
+                      float* potentials, tcs_solve_info* info);
+/* Whole class path: setInputCloud (already uploaded) + setSeeds + segment
+ * (impl/random_walker_segmentation.hpp:82-224), or the CLI pipeline for preset = TCS_PRESET_CLI.
+ * point_cluster: n int32 = cluster index of every input point (0..K-1 by ascending seed label, K = unlabelled);
+ * vertex_colour: V uint32.  Either may be NULL: results then stay on the device (tcs_graph_d_*).
+ * The graph is returned in *out (caller destroys it). */
+int tcs_segment_cloud(tcs_ctx* ctx, float resolution, int preset, int mode, const float* seed_xyz,
+                      const uint32_t* seed_label, size_t ns, const tcs_solver_opts* opts, int32_t* point_cluster,
+                      uint32_t* vertex_colour, tcs_solve_info* info, tcs_graph** out);
+/* potentials kept by store_potentials (getPotentials, random_walker_segmentation.h:251): V x K column-major */
+int tcs_graph_download_potentials(tcs_graph* g, float* potentials);
+int tcs_graph_download_colours(tcs_graph* g, uint32_t* colours);
+/* device-resident results (valid until the graph is destroyed) */
+const uint32_t* tcs_graph_d_colours(const tcs_graph* g);
+const int32_t* tcs_graph_d_point_cluster(const tcs_graph* g);
+
+/* ---- measurement hooks (bench.py): the CG SpMM kernel alone on the assembled system of the last solve ----- */
+/* launches the SpMM `reps` times on the context stream between two CUDA events; returns average ms per launch */
+int tcs_bench_spmm(tcs_graph* g, int reps, float* avg_ms, long long* algorithmic_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TCS_B200_H */

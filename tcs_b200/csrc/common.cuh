@@ -1,0 +1,158 @@
+// tcs_b200/csrc/common.cuh - internal structures of libtcs_b200.so (context, device graph, helpers).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/tcs_b200.h"
+
+#define TCS_NIL 0xFFFFFFFFu
+
+struct tcs_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  int sm_count = 148;
+  long long launches = 0;
+  std::string err;
+  // input cloud: n records {x, y, z, rgba bits}
+  float4* d_cloud = nullptr;
+  bool own_cloud = false;
+  size_t cloud_cap = 0;
+  size_t n_points = 0;
+  bool has_color = false;
+  // scratch for host<->device scalars (pinned)
+  void* h_pin = nullptr;  // 4 KB pinned
+  void* d_scal = nullptr; // 4 KB device
+  // staging buffers for uploads
+  void* d_stage = nullptr;
+  size_t stage_cap = 0;
+  cudaEvent_t ev[32];
+};
+
+int tcs_fail(tcs_ctx* ctx, int code, const char* fmt, ...);
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t _e = (call);                                                                       \
+    if (_e != cudaSuccess)                                                                         \
+      return tcs_fail(ctx, TCS_ERR_CUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e)); \
+  } while (0)
+
+#define TRY(call)            \
+  do {                       \
+    int _s = (call);         \
+    if (_s != TCS_OK) return _s; \
+  } while (0)
+
+// stream-ordered device buffer
+template <typename T>
+struct DBuf {
+  T* p = nullptr;
+  size_t n = 0;
+  tcs_ctx* ctx = nullptr;
+  DBuf() {}
+  DBuf(const DBuf&) = delete;
+  DBuf& operator=(const DBuf&) = delete;
+  ~DBuf() { release(); }
+  int alloc(tcs_ctx* c, size_t count) {
+    release();
+    ctx = c;
+    n = count;
+    if (count == 0) return TCS_OK;
+    cudaError_t e = cudaMallocAsync((void**)&p, count * sizeof(T), c->stream);
+    if (e != cudaSuccess) {
+      p = nullptr;
+      return tcs_fail(c, TCS_ERR_CUDA, "cudaMallocAsync(%zu bytes): %s", count * sizeof(T), cudaGetErrorString(e));
+    }
+    return TCS_OK;
+  }
+  void release() {
+    if (p && ctx) cudaFreeAsync(p, ctx->stream);
+    p = nullptr;
+    n = 0;
+  }
+  void swap(DBuf& o) {
+    std::swap(p, o.p);
+    std::swap(n, o.n);
+    std::swap(ctx, o.ctx);
+  }
+};
+
+// assembled random-walker system (kept for getPotentials / tcs_bench_spmm)
+struct tcs_system {
+  int n = 0;          // rows
+  int K = 0;          // label columns
+  int Kp = 0;         // padded column count used by the kernels (multiple of 4)
+  long long nnz_off = 0;
+  DBuf<uint32_t> rowptr;  // n+1
+  DBuf<int> col;          // nnz_off (row indices)
+  DBuf<float> val;        // nnz_off (-w)
+  DBuf<float> diag;       // n (degree)
+  DBuf<float> B;          // n x Kp row-major
+  DBuf<uint32_t> row_vertex;  // n
+  DBuf<int> row_of;       // V (-1 for non-rows)
+  DBuf<double> X;         // n x Kp fp64
+  DBuf<float> P, R, AP;   // n x Kp
+};
+
+struct tcs_graph {
+  tcs_ctx* ctx = nullptr;
+  size_t V = 0, E = 0, N = 0;
+  bool has_color = false;
+  bool from_builder = false;
+  int depth = 0;
+  double bbmin[3] = {0, 0, 0};
+  // vertex bundle (PointXYZRGBNormal / PointNormal fields), SoA
+  DBuf<float> x, y, z, nx, ny, nz, nw, curv;
+  DBuf<uint32_t> rgba;
+  DBuf<uint32_t> keys;  // 3 per vertex (builder graphs)
+  // global edge list in insertion order
+  DBuf<uint32_t> esrc, etgt;
+  DBuf<float> ew;
+  // out-edge lists (insertion order == ascending edge id)
+  DBuf<uint32_t> rowptr, col, eid;
+  DBuf<uint32_t> p2v;  // N
+  DBuf<int32_t> comp;  // V
+  int ncomp = -1;
+  // results
+  DBuf<uint32_t> colours;        // V
+  DBuf<int32_t> point_cluster;   // N
+  DBuf<float> potentials;        // V x K column-major (store_potentials)
+  int pot_K = 0;
+  tcs_system sys;
+};
+
+static inline unsigned div_up(size_t a, unsigned b) { return (unsigned)((a + b - 1) / b); }
+
+#define LAUNCH(ctx, kernel, grid, block, smem, ...)                        \
+  do {                                                                     \
+    kernel<<<(grid), (block), (smem), (ctx)->stream>>>(__VA_ARGS__);       \
+    (ctx)->launches++;                                                     \
+  } while (0)
+
+// ---- stage entry points shared between translation units ---------------------------------------------------
+int tcs_impl_scan_u32(tcs_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, size_t n);  // exclusive sum, d_out[n] = total (n+1 outputs)
+int tcs_impl_read_u32(tcs_ctx* ctx, const uint32_t* d_ptr, uint32_t* out);             // synchronising scalar read
+int tcs_impl_build_out_edges(tcs_graph* g);                                              // CSR from an edge list (user graphs / REMOVE policy)
+int tcs_impl_alloc_vertices(tcs_graph* g, size_t V);
+// stable LSD radix sorts (CUB) on bits [0, end_bit)
+int tcs_impl_sort_pairs_u32(tcs_ctx* ctx, uint32_t* key_in, uint32_t* key_out, uint32_t* val_in, uint32_t* val_out,
+                            size_t n, int end_bit);
+int tcs_impl_sort_pairs_u64(tcs_ctx* ctx, uint64_t* key_in, uint64_t* key_out, uint32_t* val_in, uint32_t* val_out,
+                            size_t n, int end_bit);
+
+// solve.cu / pcg.cu
+int tcs_impl_components(tcs_graph* g);
+int tcs_impl_nearest_vertices(tcs_graph* g, const float* seed_xyz, size_t ns, DBuf<int32_t>& d_nearest);
+int tcs_impl_paint_seeds(tcs_graph* g, const DBuf<int32_t>& nearest, const uint32_t* h_colour, size_t ns);
+int tcs_impl_assemble(tcs_graph* g, int K);
+// PCG + argmax on g->colours (device, seeds in / labels out); fills info (may be NULL)
+int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts, tcs_solve_info* info);
+int tcs_impl_point_clusters(tcs_graph* g, int K);

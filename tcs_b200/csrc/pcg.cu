@@ -1,0 +1,481 @@
+// tcs_b200/csrc/pcg.cu - the random-walker linear solve: multi-right-hand-side Jacobi-preconditioned CG.
+// Replaces RandomWalker::solveLinearSystem / assignColors / getPotentials (impl/random_walker.hpp:186-243):
+// Eigen::SimplicialCholesky<SparseMatrix<float>, Lower> becomes PCG over all label columns at once.
+//
+// Data layout (HBM): CSR of the off-diagonal part of L (int32 row indices, fp32 values = -w), fp32 diagonal,
+// dense blocks P, R, AP as n x Kp fp32 row-major (Kp = K rounded up to 4 => one row = Kp/4 float4), X as n x Kp
+// fp64.  Precision recipe: fp32 matrix and direction/residual vectors, fp64 dot products, fp64
+// solution, float64 true-residual replacement every `check_every` iterations.
+#include <cfloat>
+#include <cmath>
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace {
+
+__device__ __forceinline__ bool is_pow2(int q) { return (q & (q - 1)) == 0; }
+
+// Block-level reduction of per-thread partial sums of 4 columns (column group q of Q) into gout[Kp].
+__device__ __forceinline__ void reduce_columns(double acc[4], int q, int Q, bool active, double* sm, double* gout) {
+  const int Kp = 4 * Q;
+  for (int i = threadIdx.x; i < Kp; i += blockDim.x) sm[i] = 0.0;
+  __syncthreads();
+  if (is_pow2(Q) && Q <= 32) {
+    for (int o = 16; o >= Q; o >>= 1) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[j] += __shfl_xor_sync(0xFFFFFFFFu, acc[j], o);
+    }
+    if ((threadIdx.x & 31) < Q) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) atomicAdd(&sm[4 * q + j], acc[j]);
+    }
+  } else if (active) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) atomicAdd(&sm[4 * q + j], acc[j]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < Kp; i += blockDim.x)
+    if (sm[i] != 0.0) atomicAdd(&gout[i], sm[i]);
+}
+
+// ---- the CG SpMM: AP = L P over all label columns, fused p.Ap partial dots -------------------------------------
+// Q = Kp/4 consecutive threads own one row (one float4 of the row each): the gather of a neighbour's P row is one
+// contiguous 16*Q-byte read per row group.  Grid-stride over row groups; fp64 dot accumulation per thread.
+__global__ void __launch_bounds__(256) k_spmm(int n, int Q, const uint32_t* __restrict__ rowptr,
+                                              const int* __restrict__ col, const float* __restrict__ val,
+                                              const float* __restrict__ diag, const float4* __restrict__ P,
+                                              float4* __restrict__ AP, double* __restrict__ pAp) {
+  extern __shared__ double sm[];
+  const int rows_per_block = blockDim.x / Q;
+  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  const bool active = local < rows_per_block;
+  double acc[4] = {0.0, 0.0, 0.0, 0.0};
+  if (active) {
+    for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+      uint32_t a = rowptr[row];
+      const uint32_t a1 = rowptr[row + 1];
+      const float4 p = P[(size_t)row * Q + q];
+      const float d = diag[row];
+      float4 y = make_float4(d * p.x, d * p.y, d * p.z, d * p.w);
+      for (; a + 4 <= a1; a += 4) {
+        int c0 = col[a], c1 = col[a + 1], c2 = col[a + 2], c3 = col[a + 3];
+        float w0 = val[a], w1 = val[a + 1], w2 = val[a + 2], w3 = val[a + 3];
+        float4 t0 = P[(size_t)c0 * Q + q], t1 = P[(size_t)c1 * Q + q];
+        float4 t2 = P[(size_t)c2 * Q + q], t3 = P[(size_t)c3 * Q + q];
+        y.x += w0 * t0.x; y.y += w0 * t0.y; y.z += w0 * t0.z; y.w += w0 * t0.w;
+        y.x += w1 * t1.x; y.y += w1 * t1.y; y.z += w1 * t1.z; y.w += w1 * t1.w;
+        y.x += w2 * t2.x; y.y += w2 * t2.y; y.z += w2 * t2.z; y.w += w2 * t2.w;
+        y.x += w3 * t3.x; y.y += w3 * t3.y; y.z += w3 * t3.z; y.w += w3 * t3.w;
+      }
+      for (; a < a1; ++a) {
+        int c = col[a];
+        float w = val[a];
+        float4 t = P[(size_t)c * Q + q];
+        y.x += w * t.x; y.y += w * t.y; y.z += w * t.z; y.w += w * t.w;
+      }
+      AP[(size_t)row * Q + q] = y;
+      acc[0] += (double)p.x * (double)y.x; acc[1] += (double)p.y * (double)y.y;
+      acc[2] += (double)p.z * (double)y.z; acc[3] += (double)p.w * (double)y.w;
+    }
+  }
+  reduce_columns(acc, q, Q, active, sm, pAp);
+}
+
+// x = 0, r = b, p = D^-1 b, rz = sum b^2 / d, bb = sum b^2
+__global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __restrict__ B,
+                                                  const float* __restrict__ diag, float4* __restrict__ R,
+                                                  float4* __restrict__ P, double* __restrict__ X,
+                                                  double* __restrict__ rz, double* __restrict__ bb) {
+  extern __shared__ double sm[];
+  const int rows_per_block = blockDim.x / Q;
+  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  const bool active = local < rows_per_block;
+  double a_rz[4] = {0, 0, 0, 0}, a_bb[4] = {0, 0, 0, 0};
+  if (active) {
+    for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+      const size_t i = (size_t)row * Q + q;
+      const float4 b = B[i];
+      const float inv = 1.0f / diag[row];
+      R[i] = b;
+      P[i] = make_float4(b.x * inv, b.y * inv, b.z * inv, b.w * inv);
+      double2* x = (double2*)(X + 4 * i);
+      x[0] = make_double2(0.0, 0.0);
+      x[1] = make_double2(0.0, 0.0);
+      const double di = (double)inv;
+      a_bb[0] += (double)b.x * b.x; a_bb[1] += (double)b.y * b.y; a_bb[2] += (double)b.z * b.z; a_bb[3] += (double)b.w * b.w;
+      a_rz[0] += (double)b.x * b.x * di; a_rz[1] += (double)b.y * b.y * di;
+      a_rz[2] += (double)b.z * b.z * di; a_rz[3] += (double)b.w * b.w * di;
+    }
+  }
+  reduce_columns(a_rz, q, Q, active, sm, rz);
+  __syncthreads();
+  reduce_columns(a_bb, q, Q, active, sm, bb);
+}
+
+// alpha = rz / pAp ; x += alpha p ; r -= alpha Ap ; rz_next += r . D^-1 r
+__global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* __restrict__ P,
+                                                    const float4* __restrict__ AP, float4* __restrict__ R,
+                                                    double* __restrict__ X, const float* __restrict__ diag,
+                                                    const double* __restrict__ rz, const double* __restrict__ pAp,
+                                                    double* __restrict__ rz_next) {
+  extern __shared__ double sm[];
+  const int rows_per_block = blockDim.x / Q;
+  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  const bool active = local < rows_per_block;
+  double acc[4] = {0, 0, 0, 0};
+  if (active) {
+    double al[4];
+    float alf[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      double den = pAp[4 * q + j], num = rz[4 * q + j];
+      al[j] = (den > 0.0 && num > 0.0) ? num / den : 0.0;
+      alf[j] = (float)al[j];
+    }
+    for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+      const size_t i = (size_t)row * Q + q;
+      const float4 p = P[i], ap = AP[i];
+      float4 r = R[i];
+      double2* xp = (double2*)(X + 4 * i);
+      double2 x0 = xp[0], x1 = xp[1];
+      x0.x += al[0] * (double)p.x; x0.y += al[1] * (double)p.y;
+      x1.x += al[2] * (double)p.z; x1.y += al[3] * (double)p.w;
+      xp[0] = x0; xp[1] = x1;
+      r.x -= alf[0] * ap.x; r.y -= alf[1] * ap.y; r.z -= alf[2] * ap.z; r.w -= alf[3] * ap.w;
+      R[i] = r;
+      const double di = 1.0 / (double)diag[row];
+      acc[0] += (double)r.x * r.x * di; acc[1] += (double)r.y * r.y * di;
+      acc[2] += (double)r.z * r.z * di; acc[3] += (double)r.w * r.w * di;
+    }
+  }
+  reduce_columns(acc, q, Q, active, sm, rz_next);
+}
+
+// beta = rz_next / rz ; p = D^-1 r + beta p ; block 0 clears the accumulators of the coming iterations
+__global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __restrict__ R, float4* __restrict__ P,
+                                                 const float* __restrict__ diag, const double* __restrict__ rz,
+                                                 const double* __restrict__ rz_next, double* __restrict__ clear_a,
+                                                 double* __restrict__ clear_b) {
+  const int rows_per_block = blockDim.x / Q;
+  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  if (blockIdx.x == 0)
+    for (int i = threadIdx.x; i < 4 * Q; i += blockDim.x) { clear_a[i] = 0.0; clear_b[i] = 0.0; }
+  if (local >= rows_per_block) return;
+  float be[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    double den = rz[4 * q + j], num = rz_next[4 * q + j];
+    be[j] = (den > 0.0) ? (float)(num / den) : 0.0f;
+  }
+  for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+    const size_t i = (size_t)row * Q + q;
+    const float4 r = R[i];
+    float4 p = P[i];
+    const float inv = 1.0f / diag[row];
+    p.x = r.x * inv + be[0] * p.x; p.y = r.y * inv + be[1] * p.y;
+    p.z = r.z * inv + be[2] * p.z; p.w = r.w * inv + be[3] * p.w;
+    P[i] = p;
+  }
+}
+
+// float64 true residual r = b - L x (replaces the recurrence residual), rr = ||r||^2, rz = r . D^-1 r
+__global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint32_t* __restrict__ rowptr,
+                                                       const int* __restrict__ col, const float* __restrict__ val,
+                                                       const float* __restrict__ diag, const float4* __restrict__ B,
+                                                       const double* __restrict__ X, float4* __restrict__ R,
+                                                       double* __restrict__ rr, double* __restrict__ rz) {
+  extern __shared__ double sm[];
+  const int rows_per_block = blockDim.x / Q;
+  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  const bool active = local < rows_per_block;
+  double a_rr[4] = {0, 0, 0, 0}, a_rz[4] = {0, 0, 0, 0};
+  if (active) {
+    for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+      const size_t i = (size_t)row * Q + q;
+      const double d = (double)diag[row];
+      const double2* xp = (const double2*)(X + 4 * i);
+      double2 x0 = xp[0], x1 = xp[1];
+      double y[4] = {d * x0.x, d * x0.y, d * x1.x, d * x1.y};
+      for (uint32_t a = rowptr[row]; a < rowptr[row + 1]; ++a) {
+        const double w = (double)val[a];
+        const double2* t = (const double2*)(X + 4 * ((size_t)col[a] * Q + q));
+        double2 t0 = t[0], t1 = t[1];
+        y[0] += w * t0.x; y[1] += w * t0.y; y[2] += w * t1.x; y[3] += w * t1.y;
+      }
+      const float4 b = B[i];
+      double r[4] = {(double)b.x - y[0], (double)b.y - y[1], (double)b.z - y[2], (double)b.w - y[3]};
+      float4 rf = make_float4((float)r[0], (float)r[1], (float)r[2], (float)r[3]);
+      R[i] = rf;
+      const double di = 1.0 / d;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) a_rr[j] += r[j] * r[j];
+      a_rz[0] += (double)rf.x * rf.x * di; a_rz[1] += (double)rf.y * rf.y * di;
+      a_rz[2] += (double)rf.z * rf.z * di; a_rz[3] += (double)rf.w * rf.w * di;
+    }
+  }
+  reduce_columns(a_rr, q, Q, active, sm, rr);
+  __syncthreads();
+  reduce_columns(a_rz, q, Q, active, sm, rz);
+}
+
+// assignColors (impl/random_walker.hpp:209-222): first maximal potential of the row; rows whose potentials are all
+// zero (seedless components, :191-192) stay unlabelled.  Also scatters potentials (getPotentials, :224-243).
+__global__ void k_argmax(int n, int K, int Kp, const double* __restrict__ X, const uint32_t* __restrict__ row_vertex,
+                         uint32_t* __restrict__ colours, float* __restrict__ potentials, size_t V,
+                         unsigned long long* __restrict__ near_ties) {
+  int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const double* x = X + (size_t)r * Kp;
+  const uint32_t v = row_vertex[r];
+  float best = (float)x[0], second = -INFINITY;
+  int bi = 0;
+  bool any = best != 0.0f;
+  if (potentials) potentials[v] = best;
+  for (int k = 1; k < K; ++k) {
+    float f = (float)x[k];
+    if (potentials) potentials[(size_t)k * V + v] = f;
+    any = any || f != 0.0f;
+    if (f > best) { second = best; best = f; bi = k; }
+    else if (f > second) second = f;
+  }
+  if (any) {
+    colours[v] = (uint32_t)bi + 1u;
+    if (K > 1 && best - second < 1e-6f) atomicAdd(near_ties, 1ull);
+  }
+}
+
+__global__ void k_seed_potentials(size_t V, const uint32_t* __restrict__ seed_colour, float* __restrict__ potentials) {
+  size_t v = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (v >= V) return;
+  uint32_t c = seed_colour[v];
+  if (c) potentials[(size_t)(c - 1) * V + v] = 1.0f;
+}
+
+}  // namespace
+
+extern "C" void tcs_solver_opts_default(tcs_solver_opts* o) {
+  if (!o) return;
+  o->tolerance = 1e-6;
+  o->max_iterations = 200000;
+  o->check_every = 50;
+  o->store_potentials = 0;
+  o->time_spmm = 0;
+}
+
+namespace {
+
+struct PcgLaunch {
+  unsigned grid, block;
+  size_t smem;
+};
+
+PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q) {
+  PcgLaunch L;
+  L.block = 256;
+  const int rows_per_block = 256 / Q;
+  unsigned need = (unsigned)((n + rows_per_block - 1) / rows_per_block);
+  // persistent-style grid: a multiple of the SM count, 8 resident CTAs of 256 threads per SM
+  L.grid = std::max(1u, std::min(need, (unsigned)ctx->sm_count * 8u));
+  L.smem = (size_t)4 * Q * sizeof(double);
+  return L;
+}
+
+}  // namespace
+
+int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, tcs_solve_info* info) {
+  tcs_ctx* ctx = g->ctx;
+  tcs_solver_opts opts;
+  tcs_solver_opts_default(&opts);
+  if (opts_in) opts = *opts_in;
+  if (opts.check_every < 1) opts.check_every = 50;
+  if (K < 0 || K > TCS_MAX_LABELS) return tcs_fail(ctx, TCS_ERR_INPUT, "number of labels %d outside 0..%d", K, TCS_MAX_LABELS);
+  const size_t V = g->V;
+  if (info) {
+    float keep[12];
+    memcpy(keep, info->stage_ms, sizeof keep);
+    memset(info, 0, sizeof *info);
+    memcpy(info->stage_ms, keep, sizeof keep);
+    info->converged = 1;
+    info->ncolours = K;
+    info->ncomponents = g->ncomp;
+  }
+  if (V == 0 || K == 0) return TCS_OK;
+  cudaEvent_t e_asm0 = ctx->ev[8], e_asm1 = ctx->ev[9], e_solve1 = ctx->ev[10], e_arg1 = ctx->ev[11];
+  CK(cudaEventRecord(e_asm0, ctx->stream));
+  TRY(tcs_impl_assemble(g, K));
+  CK(cudaEventRecord(e_asm1, ctx->stream));
+  tcs_system& S = g->sys;
+  const int n = S.n, Kp = S.Kp, Q = Kp / 4;
+  if (info) { info->rows = n; info->nnz = S.nnz_off + n; }
+
+  float* d_pot = nullptr;
+  if (opts.store_potentials) {
+    TRY(g->potentials.alloc(ctx, V * (size_t)K));
+    g->pot_K = K;
+    CK(cudaMemsetAsync(g->potentials.p, 0, V * (size_t)K * 4, ctx->stream));
+    LAUNCH(ctx, k_seed_potentials, div_up(V, 256), 256, 0, V, g->colours.p, g->potentials.p);
+    d_pot = g->potentials.p;
+  } else {
+    g->potentials.release();
+    g->pot_K = 0;
+  }
+
+  int iterations = 0, converged = 1;
+  double rel[TCS_MAX_LABELS] = {0};
+  float spmm_sum_ms = 0.f;
+  int spmm_timed = 0, spmm_launches = 0;
+  if (n > 0) {
+    const size_t nk = (size_t)n * Kp;
+    TRY(S.X.alloc(ctx, nk)); TRY(S.P.alloc(ctx, nk)); TRY(S.R.alloc(ctx, nk)); TRY(S.AP.alloc(ctx, nk));
+    // scalar accumulators: pAp[3][Kp], rz[3][Kp], rr[Kp], bb[Kp]
+    DBuf<double> scal;
+    TRY(scal.alloc(ctx, (size_t)8 * Kp));
+    CK(cudaMemsetAsync(scal.p, 0, (size_t)8 * Kp * 8, ctx->stream));
+    double* d_pAp = scal.p;
+    double* d_rz = scal.p + 3 * Kp;
+    double* d_rr = scal.p + 6 * Kp;
+    double* d_bb = scal.p + 7 * Kp;
+    const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
+    const float4* B4 = (const float4*)S.B.p;
+    float4* P4 = (float4*)S.P.p;
+    float4* R4 = (float4*)S.R.p;
+    float4* AP4 = (float4*)S.AP.p;
+    LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Q, B4, S.diag.p, R4, P4, S.X.p, d_rz, d_bb);
+    std::vector<double> h(2 * Kp);
+    // sampled SpMM timing: one event pair every `stride` launches
+    const int kMaxSamples = 64;
+    std::vector<cudaEvent_t> evs;
+    if (opts.time_spmm) {
+      evs.resize(2 * kMaxSamples);
+      for (auto& e : evs) CK(cudaEventCreate(&e));
+    }
+    int sample_stride = 1, samples = 0;
+    converged = 0;
+    int it = 0;
+    while (it < opts.max_iterations) {
+      const int chunk = std::min(opts.check_every, opts.max_iterations - it);
+      for (int j = 0; j < chunk; ++j, ++it) {
+        const int s0 = it % 3, s1 = (it + 1) % 3, s2 = (it + 2) % 3;
+        const bool timed = opts.time_spmm && samples < kMaxSamples && (spmm_launches % sample_stride) == 0;
+        if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
+        LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, P4, AP4,
+               d_pAp + s0 * Kp);
+        if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
+        ++spmm_launches;
+        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Q, P4, AP4, R4, S.X.p, S.diag.p, d_rz + s0 * Kp,
+               d_pAp + s0 * Kp, d_rz + s1 * Kp);
+        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Q, R4, P4, S.diag.p, d_rz + s0 * Kp, d_rz + s1 * Kp,
+               d_pAp + s1 * Kp, d_rz + s2 * Kp);
+      }
+      if (opts.time_spmm && samples == kMaxSamples && sample_stride == 1) {
+        // keep the first samples; later launches are not timed (the kernel's duration does not depend on `it`)
+        sample_stride = 1 << 30;
+      }
+      // float64 true residual replaces the recurrence residual; rz of the coming iteration is recomputed from it
+      CK(cudaMemsetAsync(d_rr, 0, (size_t)Kp * 8, ctx->stream));
+      CK(cudaMemsetAsync(d_rz + (it % 3) * Kp, 0, (size_t)Kp * 8, ctx->stream));
+      LAUNCH(ctx, k_true_residual, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, B4, S.X.p, R4,
+             d_rr, d_rz + (it % 3) * Kp);
+      CK(cudaMemcpyAsync(ctx->h_pin, d_rr, (size_t)2 * Kp * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+      memcpy(h.data(), ctx->h_pin, (size_t)2 * Kp * 8);
+      bool all = true;
+      for (int k = 0; k < K; ++k) {
+        double rr = h[k], bb = h[Kp + k];
+        rel[k] = bb > 0.0 ? std::sqrt(rr / bb) : 0.0;
+        if (!(rel[k] <= opts.tolerance)) all = false;
+      }
+      if (all) { converged = 1; break; }
+    }
+    iterations = it;
+    CK(cudaEventRecord(e_solve1, ctx->stream));
+    DBuf<unsigned long long> ties;
+    TRY(ties.alloc(ctx, 1));
+    CK(cudaMemsetAsync(ties.p, 0, 8, ctx->stream));
+    LAUNCH(ctx, k_argmax, div_up(n, 256), 256, 0, n, K, Kp, S.X.p, S.row_vertex.p, g->colours.p, d_pot, V, ties.p);
+    CK(cudaEventRecord(e_arg1, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->h_pin, ties.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (info) info->near_ties = (long long)*(unsigned long long*)ctx->h_pin;
+    for (int sidx = 0; sidx < samples; ++sidx) {
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, evs[2 * sidx], evs[2 * sidx + 1]));
+      spmm_sum_ms += ms;
+      ++spmm_timed;
+    }
+    for (auto& e : evs) cudaEventDestroy(e);
+    if (info) {
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, e_asm0, e_asm1)); info->stage_ms[8] = ms;
+      CK(cudaEventElapsedTime(&ms, e_asm1, e_solve1)); info->stage_ms[9] = ms; info->solve_ms = ms;
+      CK(cudaEventElapsedTime(&ms, e_solve1, e_arg1)); info->stage_ms[10] = ms;
+    }
+    // the work vectors are only needed again by tcs_bench_spmm, which re-allocates them
+    S.R.release(); S.AP.release();
+  }
+  if (info) {
+    info->iterations = iterations;
+    info->converged = converged;
+    for (int k = 0; k < K; ++k) info->rel_residual[k] = rel[k];
+    info->spmm_launches = spmm_launches;
+    info->spmm_ms = spmm_timed ? spmm_sum_ms / spmm_timed * spmm_launches : 0.f;
+  }
+  CK(cudaGetLastError());
+  if (!converged) return tcs_fail(ctx, TCS_ERR_NOT_CONVERGED, "PCG did not reach %.1e in %d iterations", opts.tolerance, iterations);
+  return TCS_OK;
+}
+
+extern "C" int tcs_random_walker(tcs_graph* g, uint32_t* colours, int ncolours, const tcs_solver_opts* opts,
+                                 float* potentials, tcs_solve_info* info) {
+  if (!g || (g->V && !colours)) return TCS_ERR_INPUT;
+  tcs_ctx* ctx = g->ctx;
+  CK(cudaSetDevice(ctx->device));
+  const size_t V = g->V;
+  for (size_t v = 0; v < V; ++v)
+    if (colours[v] > (uint32_t)ncolours) return tcs_fail(ctx, TCS_ERR_INPUT, "colour %u of vertex %zu exceeds ncolours", colours[v], v);
+  TRY(g->colours.alloc(ctx, V));
+  if (V) CK(cudaMemcpyAsync(g->colours.p, colours, 4 * V, cudaMemcpyHostToDevice, ctx->stream));
+  tcs_solver_opts o;
+  tcs_solver_opts_default(&o);
+  if (opts) o = *opts;
+  if (potentials) o.store_potentials = 1;
+  int st = tcs_impl_random_walker(g, ncolours, &o, info);
+  if (st != TCS_OK && st != TCS_ERR_NOT_CONVERGED) return st;
+  if (V) CK(cudaMemcpyAsync(colours, g->colours.p, 4 * V, cudaMemcpyDeviceToHost, ctx->stream));
+  if (potentials && V && ncolours) CK(cudaMemcpyAsync(potentials, g->potentials.p, 4 * V * (size_t)ncolours, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return st;
+}
+
+// bench hook: the SpMM alone on the system of the last solve, `reps` launches between two events
+extern "C" int tcs_bench_spmm(tcs_graph* g, int reps, float* avg_ms, long long* algorithmic_bytes) {
+  if (!g || reps < 1) return TCS_ERR_INPUT;
+  tcs_ctx* ctx = g->ctx;
+  tcs_system& S = g->sys;
+  if (S.n == 0 || !S.P.p) return tcs_fail(ctx, TCS_ERR_STATE, "no assembled system (run the random walker first)");
+  CK(cudaSetDevice(ctx->device));
+  const int n = S.n, Kp = S.Kp, Q = Kp / 4;
+  TRY(S.AP.alloc(ctx, (size_t)n * Kp));
+  DBuf<double> acc;
+  TRY(acc.alloc(ctx, Kp));
+  CK(cudaMemsetAsync(acc.p, 0, (size_t)Kp * 8, ctx->stream));
+  const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
+  for (int i = 0; i < 3; ++i)
+    LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, (const float4*)S.P.p,
+           (float4*)S.AP.p, acc.p);
+  CK(cudaEventRecord(ctx->ev[12], ctx->stream));
+  for (int i = 0; i < reps; ++i)
+    LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, (const float4*)S.P.p,
+           (float4*)S.AP.p, acc.p);
+  CK(cudaEventRecord(ctx->ev[13], ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, ctx->ev[12], ctx->ev[13]));
+  if (avg_ms) *avg_ms = ms / reps;
+  // B_spmm = 8 nnz + 4 (n + 1) + 4 n K + 4 n K, nnz counting the diagonal, K = label columns
+  if (algorithmic_bytes)
+    *algorithmic_bytes = 8ll * (S.nnz_off + n) + 4ll * (n + 1) + 8ll * (long long)n * S.K;
+  S.AP.release();
+  return TCS_OK;
+}
