@@ -9,6 +9,7 @@
 #include <cfloat>
 #include <cmath>
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -118,7 +119,7 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
                                                     const float4* __restrict__ AP, float4* __restrict__ R,
                                                     double* __restrict__ X, const float* __restrict__ diag,
                                                     const double* __restrict__ rz, const double* __restrict__ pAp,
-                                                    double* __restrict__ rz_next) {
+                                                    double* __restrict__ rz_next, const int* __restrict__ frozen) {
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -130,7 +131,8 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       double den = pAp[4 * q + j], num = rz[4 * q + j];
-      al[j] = (den > 0.0 && num > 0.0) ? num / den : 0.0;
+      // a column that reached the tolerance is frozen: iterating on it further only amplifies rounding noise
+      al[j] = (den > 0.0 && num > 0.0 && !frozen[4 * q + j]) ? num / den : 0.0;
       alf[j] = (float)al[j];
     }
     for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
@@ -156,7 +158,7 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
 __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __restrict__ R, float4* __restrict__ P,
                                                  const float* __restrict__ diag, const double* __restrict__ rz,
                                                  const double* __restrict__ rz_next, double* __restrict__ clear_a,
-                                                 double* __restrict__ clear_b) {
+                                                 double* __restrict__ clear_b, const int* __restrict__ frozen) {
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
   if (blockIdx.x == 0)
@@ -166,7 +168,7 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     double den = rz[4 * q + j], num = rz_next[4 * q + j];
-    be[j] = (den > 0.0) ? (float)(num / den) : 0.0f;
+    be[j] = (den > 0.0 && !frozen[4 * q + j]) ? (float)(num / den) : 0.0f;
   }
   for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
     const size_t i = (size_t)row * Q + q;
@@ -336,6 +338,11 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     double* d_rz = scal.p + 3 * Kp;
     double* d_rr = scal.p + 6 * Kp;
     double* d_bb = scal.p + 7 * Kp;
+    DBuf<int> frozen;
+    TRY(frozen.alloc(ctx, Kp));
+    CK(cudaMemsetAsync(frozen.p, 0, (size_t)Kp * 4, ctx->stream));
+    int* h_frozen = (int*)((char*)ctx->h_pin + 2048);
+    for (int k = 0; k < Kp; ++k) h_frozen[k] = 0;
     const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
     const float4* B4 = (const float4*)S.B.p;
     float4* P4 = (float4*)S.P.p;
@@ -364,9 +371,9 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
         ++spmm_launches;
         LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Q, P4, AP4, R4, S.X.p, S.diag.p, d_rz + s0 * Kp,
-               d_pAp + s0 * Kp, d_rz + s1 * Kp);
+               d_pAp + s0 * Kp, d_rz + s1 * Kp, frozen.p);
         LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Q, R4, P4, S.diag.p, d_rz + s0 * Kp, d_rz + s1 * Kp,
-               d_pAp + s1 * Kp, d_rz + s2 * Kp);
+               d_pAp + s1 * Kp, d_rz + s2 * Kp, frozen.p);
       }
       if (opts.time_spmm && samples == kMaxSamples && sample_stride == 1) {
         // keep the first samples; later launches are not timed (the kernel's duration does not depend on `it`)
@@ -385,6 +392,13 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         double rr = h[k], bb = h[Kp + k];
         rel[k] = bb > 0.0 ? std::sqrt(rr / bb) : 0.0;
         if (!(rel[k] <= opts.tolerance)) all = false;
+        else h_frozen[k] = 1;
+      }
+      if (!all) CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp * 4, cudaMemcpyHostToDevice, ctx->stream));
+      if (getenv("TCS_DEBUG")) {
+        fprintf(stderr, "[tcs] it=%d rel:", it);
+        for (int k = 0; k < K; ++k) fprintf(stderr, " %.2e", rel[k]);
+        fprintf(stderr, "\n");
       }
       if (all) { converged = 1; break; }
     }
