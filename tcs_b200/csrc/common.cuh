@@ -85,6 +85,16 @@ struct DBuf {
   }
 };
 
+// tile shape of k_spmm_tiled (spmm.cuh)
+struct SpmmTile {
+  int R;        // rows per tile (multiple of 256 / Q)
+  int H;        // halo rows staged on either side
+  int cap;      // capacity of the staged CSR segment in entries (even)
+  int farcap;   // rows of the far buffer
+  // shared-memory byte offsets
+  int off_rp, off_diag, off_cv, off_p, off_red, total;
+};
+
 // assembled random-walker system (kept for getPotentials / tcs_bench_spmm)
 struct tcs_system {
   int n = 0;          // rows
@@ -100,6 +110,12 @@ struct tcs_system {
   DBuf<int> row_of;       // V (-1 for non-rows)
   DBuf<double> X;         // n x Kp fp64
   DBuf<float> P, R, AP;   // n x Kp
+  // k_spmm_tiled plan (spmm.cuh)
+  bool tiled = false;
+  SpmmTile tile;
+  DBuf<int2> cv;                  // {col or -1 - far slot, weight bits} per off-diagonal entry
+  DBuf<int> far_rows;             // per tile: de-duplicated rows outside the tile's window
+  DBuf<uint32_t> tile_far_ptr;    // ntiles + 1 offsets into far_rows
 };
 
 struct tcs_graph {

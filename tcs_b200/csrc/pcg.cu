@@ -40,6 +40,10 @@ __device__ __forceinline__ void reduce_columns(double acc[4], int q, int Q, bool
     if (sm[i] != 0.0) atomicAdd(&gout[i], sm[i]);
 }
 
+}  // namespace
+#include "spmm.cuh"
+namespace {
+
 // ---- the CG SpMM: AP = L P over all label columns, fused p.Ap partial dots -------------------------------------
 // Q = Kp/4 consecutive threads own one row (one float4 of the row each): the gather of a neighbour's P row is one
 // contiguous 16*Q-byte read per row group.  Grid-stride over row groups; fp64 dot accumulation per thread.
@@ -272,6 +276,118 @@ struct PcgLaunch {
   size_t smem;
 };
 
+__global__ void k_tile_max_nnz(int n, int R, const uint32_t* __restrict__ rowptr, uint32_t* __restrict__ out) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  int r0 = t * R;
+  if (r0 >= n) return;
+  int r1 = min(n, r0 + R);
+  atomicMax(out, rowptr[r1] - rowptr[r0]);
+}
+
+// Choose the tile shape of k_spmm_tiled for this system (two CTAs of 256 threads per SM share the 227 KB).
+int spmm_plan(tcs_ctx* ctx, tcs_system& S) {
+  S.tiled = false;
+  const char* force = getenv("TCS_SPMM");
+  if (force && !strcmp(force, "v1")) return TCS_OK;
+  const int n = S.n, Q = S.Kp / 4;
+  if (n < 8192 || S.nnz_off == 0) return TCS_OK;  // tiny systems are launch-bound, not bandwidth-bound
+  const int rows_per_pass = 256 / Q;
+  int R = getenv("TCS_TILE_R") ? atoi(getenv("TCS_TILE_R")) : 256;
+  R = std::min(508, std::max(64, (R + 3) & ~3));  // multiple of 4: the diagonal slice is a 16-byte aligned bulk copy;
+                                                   // <= 508: the rowptr prefetch holds two values per thread
+  (void)rows_per_pass;
+  uint32_t* d_max = (uint32_t*)ctx->d_scal + 16;
+  CK(cudaMemsetAsync(d_max, 0, 8, ctx->stream));
+  const int ntiles = (n + R - 1) / R;
+  LAUNCH(ctx, k_tile_max_nnz, div_up(ntiles, 256), 256, 0, n, R, S.rowptr.p, d_max);
+  uint32_t mx = 0;
+  TRY(tcs_impl_read_u32(ctx, d_max, &mx));
+  const int budget = (getenv("TCS_TILE_SMEM_KB") ? atoi(getenv("TCS_TILE_SMEM_KB")) : 110) * 1024;
+  const int rowbytes = 16 * Q;
+  SpmmTile T;
+  T.R = R;
+  T.cap = (int)((mx + 1u) & ~1u) + 4;
+  T.farcap = getenv("TCS_TILE_FAR") ? atoi(getenv("TCS_TILE_FAR")) : std::max(64, R);
+  T.off_rp = 16;
+  T.off_diag = (T.off_rp + (R + 3) * 4 + 15) & ~15;
+  T.off_cv = (T.off_diag + R * 4 + 16 + 15) & ~15;
+  T.off_red = T.off_cv + T.cap * 8;
+  T.off_p = (T.off_red + S.Kp * 8 + 127) & ~127;
+  int left = budget - T.off_p - (R + T.farcap) * rowbytes;
+  if (left < 0) return TCS_OK;  // very dense rows (user graphs): keep the generic kernel
+  int H = left / (2 * rowbytes);
+  if (getenv("TCS_TILE_H")) H = std::min(H, atoi(getenv("TCS_TILE_H")));
+  T.H = std::min(H, 4096);
+
+  // one-time resolution of the far entries: {col,val} pairs, per-tile de-duplicated far-row lists
+  const size_t nnz = (size_t)S.nnz_off;
+  TRY(S.cv.alloc(ctx, nnz + 8));
+  TRY(S.tile_far_ptr.alloc(ctx, (size_t)ntiles + 2));
+  DBuf<uint32_t> flags, pos;
+  TRY(flags.alloc(ctx, nnz + 1)); TRY(pos.alloc(ctx, nnz + 1));
+  CK(cudaMemsetAsync(S.cv.p + nnz, 0, 8 * sizeof(int2), ctx->stream));
+  LAUNCH(ctx, k_far_flags, div_up(n, 128), 128, 0, n, T.R, T.H, S.rowptr.p, S.col.p, S.val.p, S.cv.p, flags.p);
+  TRY(tcs_impl_scan_u32(ctx, flags.p, pos.p, nnz));
+  uint32_t nfar = 0;
+  TRY(tcs_impl_read_u32(ctx, pos.p + nnz, &nfar));
+  uint32_t max_far = 0, nuniq = 0;
+  if (nfar) {
+    DBuf<unsigned long long> k0, k1;
+    DBuf<uint32_t> e0, e1, head, uidx;
+    TRY(k0.alloc(ctx, nfar)); TRY(k1.alloc(ctx, nfar)); TRY(e0.alloc(ctx, nfar)); TRY(e1.alloc(ctx, nfar));
+    TRY(head.alloc(ctx, (size_t)nfar + 1)); TRY(uidx.alloc(ctx, (size_t)nfar + 1));
+    LAUNCH(ctx, k_far_scatter, div_up(n, 128), 128, 0, n, T.R, S.rowptr.p, S.col.p, flags.p, pos.p, k0.p, e0.p);
+    int tbits = 1;
+    while ((1 << tbits) < ntiles + 1) ++tbits;
+    TRY(tcs_impl_sort_pairs_u64(ctx, (uint64_t*)k0.p, (uint64_t*)k1.p, e0.p, e1.p, nfar, 32 + tbits));
+    LAUNCH(ctx, k_far_heads, div_up(nfar, 256), 256, 0, k1.p, nfar, head.p);
+    TRY(tcs_impl_scan_u32(ctx, head.p, uidx.p, nfar));
+    LAUNCH(ctx, k_far_tile_ptr, div_up(ntiles + 1, 256), 256, 0, ntiles, k1.p, nfar, uidx.p, S.tile_far_ptr.p);
+    TRY(tcs_impl_read_u32(ctx, uidx.p + nfar, &nuniq));
+    TRY(S.far_rows.alloc(ctx, (size_t)nuniq + 4));
+    LAUNCH(ctx, k_far_assign, div_up(nfar, 256), 256, 0, nfar, k1.p, e1.p, head.p, uidx.p, S.tile_far_ptr.p, S.cv.p,
+           S.far_rows.p, d_max + 1);
+    TRY(tcs_impl_read_u32(ctx, d_max + 1, &max_far));
+  } else {
+    CK(cudaMemsetAsync(S.tile_far_ptr.p, 0, ((size_t)ntiles + 2) * 4, ctx->stream));
+    TRY(S.far_rows.alloc(ctx, 4));
+  }
+  if ((int)max_far > T.farcap) T.farcap = (int)((max_far + 15u) & ~15u);
+  T.total = T.off_p + (R + 2 * T.H + T.farcap) * rowbytes;
+  if (T.total > 113 * 1024 && T.total > budget) {
+    if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] spmm tiled: far buffer of %u rows does not fit, using v1\n", max_far);
+    return TCS_OK;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(k_spmm_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+    attr_set = true;
+  }
+  S.tile = T;
+  S.tiled = true;
+  if (getenv("TCS_DEBUG"))
+    fprintf(stderr, "[tcs] spmm tiled: R=%d H=%d cap=%d farcap=%d smem=%d B (max tile nnz %u, far entries %u = %.1f%%, distinct far rows %u, max per tile %u)\n",
+            T.R, T.H, T.cap, T.farcap, T.total, mx, nfar, 100.0 * nfar / (double)nnz, nuniq, max_far);
+  return TCS_OK;
+}
+
+PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q);
+
+// AP = L P, pAp += p . Ap per column
+void launch_spmm(tcs_ctx* ctx, tcs_system& S, const float4* P4, float4* AP4, double* pAp) {
+  const int n = S.n, Q = S.Kp / 4;
+  if (S.tiled) {
+    const SpmmTile& T = S.tile;
+    const int ntiles = (n + T.R - 1) / T.R;
+    const unsigned grid = (unsigned)std::min(ntiles, 2 * ctx->sm_count);
+    LAUNCH(ctx, k_spmm_tiled, grid, 256, (size_t)T.total, n, Q, T, S.rowptr.p, S.cv.p, S.far_rows.p, S.tile_far_ptr.p,
+           S.diag.p, P4, AP4, pAp);
+  } else {
+    const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
+    LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, P4, AP4, pAp);
+  }
+}
+
 PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q) {
   PcgLaunch L;
   L.block = 256;
@@ -344,6 +460,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     int* h_frozen = (int*)((char*)ctx->h_pin + 2048);
     for (int k = 0; k < Kp; ++k) h_frozen[k] = 0;
     const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
+    TRY(spmm_plan(ctx, S));
     const float4* B4 = (const float4*)S.B.p;
     float4* P4 = (float4*)S.P.p;
     float4* R4 = (float4*)S.R.p;
@@ -366,8 +483,8 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         const int s0 = it % 3, s1 = (it + 1) % 3, s2 = (it + 2) % 3;
         const bool timed = opts.time_spmm && samples < kMaxSamples && (spmm_launches % sample_stride) == 0;
         if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
-        LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, P4, AP4,
-               d_pAp + s0 * Kp);
+        launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp);
+        ctx->launches += 0;
         if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
         ++spmm_launches;
         LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Q, P4, AP4, R4, S.X.p, S.diag.p, d_rz + s0 * Kp,
@@ -475,13 +592,9 @@ extern "C" int tcs_bench_spmm(tcs_graph* g, int reps, float* avg_ms, long long* 
   TRY(acc.alloc(ctx, Kp));
   CK(cudaMemsetAsync(acc.p, 0, (size_t)Kp * 8, ctx->stream));
   const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
-  for (int i = 0; i < 3; ++i)
-    LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, (const float4*)S.P.p,
-           (float4*)S.AP.p, acc.p);
+  for (int i = 0; i < 3; ++i) launch_spmm(ctx, S, (const float4*)S.P.p, (float4*)S.AP.p, acc.p);
   CK(cudaEventRecord(ctx->ev[12], ctx->stream));
-  for (int i = 0; i < reps; ++i)
-    LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, (const float4*)S.P.p,
-           (float4*)S.AP.p, acc.p);
+  for (int i = 0; i < reps; ++i) launch_spmm(ctx, S, (const float4*)S.P.p, (float4*)S.AP.p, acc.p);
   CK(cudaEventRecord(ctx->ev[13], ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   float ms = 0.f;
