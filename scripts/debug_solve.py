@@ -10,5 +10,5 @@ xyz, rgba, label = d["xyz"], d["rgba"], d["label"]
 sx, sl, _ = seeds_from_labels(xyz, label, ids[name], 5)
 ctx = capi.Context(0)
 ctx.upload_cloud(xyz, rgba)
-r = ctx.segment_cloud(0.006, sx, sl, preset=0, mode=0, opts=capi.default_opts(max_iterations=int(sys.argv[2]) if len(sys.argv) > 2 else 6000, check_every=int(sys.argv[3]) if len(sys.argv) > 3 else 50))
+r = ctx.segment_cloud(0.006, sx, sl, preset=int(os.environ.get("PRESET", "0")), mode=0, opts=capi.default_opts(max_iterations=int(sys.argv[2]) if len(sys.argv) > 2 else 6000, check_every=int(sys.argv[3]) if len(sys.argv) > 3 else 50))
 print(r["status"], r["info"].as_dict())

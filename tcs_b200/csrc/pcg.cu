@@ -87,10 +87,10 @@ __global__ void __launch_bounds__(256) k_spmm(int n, int Q, const uint32_t* __re
   reduce_columns(acc, q, Q, active, sm, pAp);
 }
 
-// x = 0, r = b, p = D^-1 b, rz = sum b^2 / d, bb = sum b^2
+// x = 0, r = b, p = D^-1 b, rz = sum b^2 / d, bb = sum b^2 ; also 1/d
 __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __restrict__ B,
-                                                  const float* __restrict__ diag, float4* __restrict__ R,
-                                                  float4* __restrict__ P, double* __restrict__ X,
+                                                  const float* __restrict__ diag, float* __restrict__ invd,
+                                                  float4* __restrict__ R, float4* __restrict__ P, double* __restrict__ X,
                                                   double* __restrict__ rz, double* __restrict__ bb) {
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __
       const size_t i = (size_t)row * Q + q;
       const float4 b = B[i];
       const float inv = 1.0f / diag[row];
+      if (q == 0) invd[row] = inv;
       R[i] = b;
       P[i] = make_float4(b.x * inv, b.y * inv, b.z * inv, b.w * inv);
       double2* x = (double2*)(X + 4 * i);
@@ -118,10 +119,11 @@ __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __
   reduce_columns(a_bb, q, Q, active, sm, bb);
 }
 
-// alpha = rz / pAp ; x += alpha p ; r -= alpha Ap ; rz_next += r . D^-1 r
+// alpha = rz / pAp ; x += alpha p (float64: an fp32 x stalls the true residual at 1e-4) ;
+// r -= alpha Ap ; rz_next += r . D^-1 r
 __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* __restrict__ P,
                                                     const float4* __restrict__ AP, float4* __restrict__ R,
-                                                    double* __restrict__ X, const float* __restrict__ diag,
+                                                    double* __restrict__ X, const float* __restrict__ invd,
                                                     const double* __restrict__ rz, const double* __restrict__ pAp,
                                                     double* __restrict__ rz_next, const int* __restrict__ frozen) {
   extern __shared__ double sm[];
@@ -130,29 +132,51 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
   const bool active = local < rows_per_block;
   double acc[4] = {0, 0, 0, 0};
   if (active) {
-    double al[4];
-    float alf[4];
+    float al[4];
+    double ald[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       double den = pAp[4 * q + j], num = rz[4 * q + j];
       // a column that reached the tolerance is frozen: iterating on it further only amplifies rounding noise
-      al[j] = (den > 0.0 && num > 0.0 && !frozen[4 * q + j]) ? num / den : 0.0;
-      alf[j] = (float)al[j];
+      ald[j] = (den > 0.0 && num > 0.0 && !frozen[4 * q + j]) ? num / den : 0.0;
+      al[j] = (float)ald[j];
     }
-    for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+    const int stride = gridDim.x * rows_per_block;
+    int row = blockIdx.x * rows_per_block + local;
+    // two rows per step: eight independent 16-byte loads in flight per thread
+    for (; row + stride < n; row += 2 * stride) {
+      const size_t i0 = (size_t)row * Q + q, i1 = (size_t)(row + stride) * Q + q;
+      const float4 p0 = P[i0], p1 = P[i1], ap0 = AP[i0], ap1 = AP[i1];
+      float4 r0 = R[i0], r1 = R[i1];
+      double2* xp0 = (double2*)(X + 4 * i0);
+      double2* xp1 = (double2*)(X + 4 * i1);
+      double2 x0a = xp0[0], x0b = xp0[1], x1a = xp1[0], x1b = xp1[1];
+      const float d0 = invd[row], d1 = invd[row + stride];
+      x0a.x += ald[0] * (double)p0.x; x0a.y += ald[1] * (double)p0.y; x0b.x += ald[2] * (double)p0.z; x0b.y += ald[3] * (double)p0.w;
+      x1a.x += ald[0] * (double)p1.x; x1a.y += ald[1] * (double)p1.y; x1b.x += ald[2] * (double)p1.z; x1b.y += ald[3] * (double)p1.w;
+      r0.x -= al[0] * ap0.x; r0.y -= al[1] * ap0.y; r0.z -= al[2] * ap0.z; r0.w -= al[3] * ap0.w;
+      r1.x -= al[0] * ap1.x; r1.y -= al[1] * ap1.y; r1.z -= al[2] * ap1.z; r1.w -= al[3] * ap1.w;
+      xp0[0] = x0a; xp0[1] = x0b; xp1[0] = x1a; xp1[1] = x1b; R[i0] = r0; R[i1] = r1;
+      // float64 products: r can sit far below sqrt(FLT_MIN) on quickly converging columns
+      const double e0 = (double)d0, e1 = (double)d1;
+      acc[0] += (double)r0.x * (double)r0.x * e0 + (double)r1.x * (double)r1.x * e1;
+      acc[1] += (double)r0.y * (double)r0.y * e0 + (double)r1.y * (double)r1.y * e1;
+      acc[2] += (double)r0.z * (double)r0.z * e0 + (double)r1.z * (double)r1.z * e1;
+      acc[3] += (double)r0.w * (double)r0.w * e0 + (double)r1.w * (double)r1.w * e1;
+    }
+    for (; row < n; row += stride) {
       const size_t i = (size_t)row * Q + q;
       const float4 p = P[i], ap = AP[i];
       float4 r = R[i];
       double2* xp = (double2*)(X + 4 * i);
-      double2 x0 = xp[0], x1 = xp[1];
-      x0.x += al[0] * (double)p.x; x0.y += al[1] * (double)p.y;
-      x1.x += al[2] * (double)p.z; x1.y += al[3] * (double)p.w;
-      xp[0] = x0; xp[1] = x1;
-      r.x -= alf[0] * ap.x; r.y -= alf[1] * ap.y; r.z -= alf[2] * ap.z; r.w -= alf[3] * ap.w;
-      R[i] = r;
-      const double di = 1.0 / (double)diag[row];
-      acc[0] += (double)r.x * r.x * di; acc[1] += (double)r.y * r.y * di;
-      acc[2] += (double)r.z * r.z * di; acc[3] += (double)r.w * r.w * di;
+      double2 xa = xp[0], xb = xp[1];
+      const float d = invd[row];
+      xa.x += ald[0] * (double)p.x; xa.y += ald[1] * (double)p.y; xb.x += ald[2] * (double)p.z; xb.y += ald[3] * (double)p.w;
+      r.x -= al[0] * ap.x; r.y -= al[1] * ap.y; r.z -= al[2] * ap.z; r.w -= al[3] * ap.w;
+      xp[0] = xa; xp[1] = xb; R[i] = r;
+      const double e = (double)d;
+      acc[0] += (double)r.x * (double)r.x * e; acc[1] += (double)r.y * (double)r.y * e;
+      acc[2] += (double)r.z * (double)r.z * e; acc[3] += (double)r.w * (double)r.w * e;
     }
   }
   reduce_columns(acc, q, Q, active, sm, rz_next);
@@ -160,7 +184,7 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
 
 // beta = rz_next / rz ; p = D^-1 r + beta p ; block 0 clears the accumulators of the coming iterations
 __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __restrict__ R, float4* __restrict__ P,
-                                                 const float* __restrict__ diag, const double* __restrict__ rz,
+                                                 const float* __restrict__ invd, const double* __restrict__ rz,
                                                  const double* __restrict__ rz_next, double* __restrict__ clear_a,
                                                  double* __restrict__ clear_b, const int* __restrict__ frozen) {
   const int rows_per_block = blockDim.x / Q;
@@ -174,13 +198,26 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
     double den = rz[4 * q + j], num = rz_next[4 * q + j];
     be[j] = (den > 0.0 && !frozen[4 * q + j]) ? (float)(num / den) : 0.0f;
   }
-  for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+  const int stride = gridDim.x * rows_per_block;
+  int row = blockIdx.x * rows_per_block + local;
+  for (; row + stride < n; row += 2 * stride) {
+    const size_t i0 = (size_t)row * Q + q, i1 = (size_t)(row + stride) * Q + q;
+    const float4 r0 = R[i0], r1 = R[i1];
+    float4 p0 = P[i0], p1 = P[i1];
+    const float d0 = invd[row], d1 = invd[row + stride];
+    p0.x = r0.x * d0 + be[0] * p0.x; p0.y = r0.y * d0 + be[1] * p0.y;
+    p0.z = r0.z * d0 + be[2] * p0.z; p0.w = r0.w * d0 + be[3] * p0.w;
+    p1.x = r1.x * d1 + be[0] * p1.x; p1.y = r1.y * d1 + be[1] * p1.y;
+    p1.z = r1.z * d1 + be[2] * p1.z; p1.w = r1.w * d1 + be[3] * p1.w;
+    P[i0] = p0; P[i1] = p1;
+  }
+  for (; row < n; row += stride) {
     const size_t i = (size_t)row * Q + q;
     const float4 r = R[i];
     float4 p = P[i];
-    const float inv = 1.0f / diag[row];
-    p.x = r.x * inv + be[0] * p.x; p.y = r.y * inv + be[1] * p.y;
-    p.z = r.z * inv + be[2] * p.z; p.w = r.w * inv + be[3] * p.w;
+    const float d = invd[row];
+    p.x = r.x * d + be[0] * p.x; p.y = r.y * d + be[1] * p.y;
+    p.z = r.z * d + be[2] * p.z; p.w = r.w * d + be[3] * p.w;
     P[i] = p;
   }
 }
@@ -446,6 +483,8 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
   if (n > 0) {
     const size_t nk = (size_t)n * Kp;
     TRY(S.X.alloc(ctx, nk)); TRY(S.P.alloc(ctx, nk)); TRY(S.R.alloc(ctx, nk)); TRY(S.AP.alloc(ctx, nk));
+    DBuf<float> invd;
+    TRY(invd.alloc(ctx, n));
     // scalar accumulators: pAp[3][Kp], rz[3][Kp], rr[Kp], bb[Kp]
     DBuf<double> scal;
     TRY(scal.alloc(ctx, (size_t)8 * Kp));
@@ -465,7 +504,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     float4* P4 = (float4*)S.P.p;
     float4* R4 = (float4*)S.R.p;
     float4* AP4 = (float4*)S.AP.p;
-    LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Q, B4, S.diag.p, R4, P4, S.X.p, d_rz, d_bb);
+    LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Q, B4, S.diag.p, invd.p, R4, P4, S.X.p, d_rz, d_bb);
     std::vector<double> h(2 * Kp);
     // sampled SpMM timing: one event pair every `stride` launches
     const int kMaxSamples = 64;
@@ -487,9 +526,9 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         ctx->launches += 0;
         if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
         ++spmm_launches;
-        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Q, P4, AP4, R4, S.X.p, S.diag.p, d_rz + s0 * Kp,
+        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Q, P4, AP4, R4, S.X.p, invd.p, d_rz + s0 * Kp,
                d_pAp + s0 * Kp, d_rz + s1 * Kp, frozen.p);
-        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Q, R4, P4, S.diag.p, d_rz + s0 * Kp, d_rz + s1 * Kp,
+        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Q, R4, P4, invd.p, d_rz + s0 * Kp, d_rz + s1 * Kp,
                d_pAp + s1 * Kp, d_rz + s2 * Kp, frozen.p);
       }
       if (opts.time_spmm && samples == kMaxSamples && sample_stride == 1) {
