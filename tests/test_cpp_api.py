@@ -1,0 +1,81 @@
+"""The C++ drop-in API (include/tcs/*.h: pcl::segmentation::RandomWalkerSegmentation, pcl::graph::*), driven through
+tests/cpp/api_check.cpp the way a caller of the reference would use it, checked against the CPU oracle."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "tcs_b200", "cpp", "api_check")
+
+
+def _build():
+    subprocess.check_call(["make", "-C", os.path.join(ROOT, "tcs_b200", "cpp"), "-s"])
+
+
+def _write_input(path, xyz, rgba, sx, sl):
+    with open(path, "wb") as f:
+        f.write(struct.pack("<Q", len(xyz)))
+        f.write(np.ascontiguousarray(xyz, np.float32).tobytes())
+        f.write(np.ascontiguousarray(rgba, np.uint32).tobytes())
+        f.write(struct.pack("<Q", len(sl)))
+        f.write(np.ascontiguousarray(sx, np.float32).tobytes())
+        f.write(np.ascontiguousarray(sl, np.uint32).tobytes())
+
+
+def _read_output(path, m):
+    raw = open(path, "rb").read()
+    cl = np.frombuffer(raw, np.int32, m)
+    off = 4 * m
+    V = struct.unpack_from("<Q", raw, off)[0]; off += 8
+    col = np.frombuffer(raw, np.uint32, V, off); off += 4 * V
+    K = struct.unpack_from("<Q", raw, off)[0]; off += 8
+    pot = np.frombuffer(raw, np.float32, V * K, off).reshape(K, V).T
+    return cl, col, pot
+
+
+def test_cpp_api_compiles_and_fails_loudly_without_gpu(tmp_path):
+    """Header-only API builds with plain g++ against the C ABI; with no CUDA device it throws, it does not fall back."""
+    import torch
+    _build()
+    assert os.path.exists(EXE)
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    inp, out = str(tmp_path / "i.bin"), str(tmp_path / "o.bin")
+    _write_input(inp, np.array([[0, 0, 1]], np.float32), np.array([0xFF000000], np.uint32),
+                 np.array([[0, 0, 1]], np.float32), np.array([1], np.uint32))
+    r = subprocess.run([EXE, "class", inp, out], capture_output=True, text=True)
+    assert r.returncode == 3 and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["class", "cli"])
+@pytest.mark.parametrize("name", ["test1", "test47"])
+def test_cpp_api_matches_oracle(scenes, tmp_path, mode, name):
+    import orc
+    from tcs_b200.seeds import seeds_from_labels
+    _build()
+    sc = scenes[name]
+    sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
+    inp, out = str(tmp_path / "i.bin"), str(tmp_path / "o.bin")
+    _write_input(inp, sc["xyz"], sc["rgba"], sx, sl)
+    r = subprocess.run([EXE, mode, inp, out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ref = orc.segment_cloud(sc["xyz"], sc["rgba"], 0.006, sx, sl, preset=0 if mode == "class" else 1,
+                            solver=orc.SOLVE_LDLT_F64)
+    V = ref["graph"].V
+    m = len(sc["xyz"]) if mode == "class" else V
+    cl, col, pot = _read_output(out, m)
+    assert len(col) == V and pot.shape == (V, ref["K"])
+    bad = int(np.count_nonzero(col != ref["vertex_colour"]))
+    assert bad <= max(3, V // 2000), bad
+    if mode == "class":
+        assert np.count_nonzero(cl != ref["point_cluster"]) <= 10 * max(1, bad)
+    else:   # graph input: clusters index vertices (impl/random_walker_segmentation.hpp:213-221)
+        expect = np.where(ref["vertex_colour"] == 0, ref["K"], ref["vertex_colour"].astype(np.int64) - 1)
+        assert np.count_nonzero(cl != expect) <= max(3, V // 2000)
+    # potentials: rows sum to 1 on labelled vertices, seeds are one-hot
+    lab = col > 0
+    np.testing.assert_allclose(pot[lab].sum(axis=1), 1.0, atol=2e-3)
