@@ -85,6 +85,7 @@ typedef struct tcs_solve_info {
   float solve_ms;               /* device time of the whole PCG loop */
   float stage_ms[12];           /* build, normals, smoothen, normals2, signs, weights, components, seeds,
                                    assemble, solve, argmax, point labels (device time, CUDA events) */
+  int spmm_kernel;              /* which SpMM ran: 1 = k_spmm (generic), 2 = k_spmm_tiled, 3 = k_spmm_ring */
 } tcs_solve_info;
 
 /* ---- context ------------------------------------------------------------------------------------------- */
@@ -170,6 +171,11 @@ const int32_t* tcs_graph_d_point_cluster(const tcs_graph* g);
 /* ---- measurement hooks (bench.py): the CG SpMM kernel alone on the assembled system of the last solve ----- */
 /* launches the SpMM `reps` times on the context stream between two CUDA events; returns average ms per launch */
 int tcs_bench_spmm(tcs_graph* g, int reps, float* avg_ms, long long* algorithmic_bytes);
+/* test hook: applies the generic SpMM kernel (k_spmm) and the kernel planned for this system (tiled / ring) to the
+ * same pseudo-random dense block and returns max |difference|, max |reference| over the n x K outputs and over the
+ * per-column p.Ap dots (relative), plus the planned kernel's id (tcs_solve_info.spmm_kernel) */
+int tcs_check_spmm(tcs_graph* g, unsigned seed, double* max_abs_diff, double* max_abs_ref, double* max_rel_dot_diff,
+                   int* kernel);
 
 #ifdef __cplusplus
 }

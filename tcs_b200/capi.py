@@ -37,7 +37,7 @@ EXPORTS = [
     "tcs_graph_upload_weights", "tcs_normals", "tcs_smoothen", "tcs_signed_curvatures", "tcs_edge_weights",
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
-    "tcs_graph_d_point_cluster", "tcs_bench_spmm",
+    "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm",
 ]
 
 
@@ -54,14 +54,15 @@ class SolveInfo(C.Structure):
     _fields_ = [("iterations", C.c_int), ("converged", C.c_int), ("rows", C.c_int), ("nnz", C.c_longlong),
                 ("ncolours", C.c_int), ("ncomponents", C.c_int), ("near_ties", C.c_longlong),
                 ("rel_residual", C.c_double * MAX_LABELS), ("spmm_ms", C.c_float), ("spmm_launches", C.c_int),
-                ("solve_ms", C.c_float), ("stage_ms", C.c_float * 12)]
+                ("solve_ms", C.c_float), ("stage_ms", C.c_float * 12), ("spmm_kernel", C.c_int)]
 
     def as_dict(self):
         K = self.ncolours
         return dict(iterations=self.iterations, converged=bool(self.converged), rows=self.rows, nnz=self.nnz,
                     ncolours=K, ncomponents=self.ncomponents, near_ties=self.near_ties,
                     rel_residual=[self.rel_residual[k] for k in range(K)], spmm_ms=self.spmm_ms,
-                    spmm_launches=self.spmm_launches, solve_ms=self.solve_ms, stage_ms=list(self.stage_ms))
+                    spmm_launches=self.spmm_launches, solve_ms=self.solve_ms, stage_ms=list(self.stage_ms),
+                    spmm_kernel=self.spmm_kernel)
 
 
 class TcsError(RuntimeError):
@@ -128,6 +129,8 @@ def lib():
     L.tcs_graph_d_point_cluster.argtypes = [vp]
     L.tcs_graph_d_point_cluster.restype = vp
     L.tcs_bench_spmm.argtypes = [vp, ci, C.POINTER(cf), C.POINTER(C.c_longlong)]
+    L.tcs_check_spmm.argtypes = [vp, C.c_uint, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                 C.POINTER(ci)]
     _lib = L
     return L
 
@@ -351,6 +354,11 @@ class Graph:
         c = np.zeros(self.V, np.uint32)
         self.ctx.check(lib().tcs_graph_download_colours(self.h, _p(c)))
         return c
+
+    def check_spmm(self, seed=1):
+        d, r, dd, k = C.c_double(), C.c_double(), C.c_double(), C.c_int()
+        self.ctx.check(lib().tcs_check_spmm(self.h, seed, C.byref(d), C.byref(r), C.byref(dd), C.byref(k)))
+        return d.value, r.value, dd.value, k.value
 
     def bench_spmm(self, reps=20):
         ms, nbytes = C.c_float(), C.c_longlong()

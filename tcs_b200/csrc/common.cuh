@@ -95,6 +95,21 @@ struct SpmmTile {
   int off_rp, off_diag, off_cv, off_p, off_red, total;
 };
 
+// shape of k_spmm_ring (spmm_ring.cuh): contiguous tile range per CTA, sliding ring window of P, S-stage TMA pipeline
+struct SpmmRing {
+  int R;          // rows per tile = consumer warps x G
+  int G;          // rows per warp step = 32 / Q
+  int H;          // halo rows on either side of a tile that are guaranteed to be in the ring
+  int S;          // pipeline stages (tiles in flight)
+  int ring_rows;  // power of two
+  int dup;        // second copy of the ring shifted by half a 128-byte line (64-byte rows only): conflict-free gathers
+  int cap;        // {offset, weight} entries per stage (multiple of 8)
+  int farcap;     // far rows per stage
+  int nctas;
+  // shared-memory byte offsets (stage-relative for rp/diag/cv/far)
+  int off_bar, off_red, off_ids, ids_bytes, off_stage0, stage_bytes, off_meta, off_cv, off_far, off_ring, ring_bytes, total;
+};
+
 // assembled random-walker system (kept for getPotentials / tcs_bench_spmm)
 struct tcs_system {
   int n = 0;          // rows
@@ -116,6 +131,15 @@ struct tcs_system {
   DBuf<int2> cv;                  // {col or -1 - far slot, weight bits} per off-diagonal entry
   DBuf<int> far_rows;             // per tile: de-duplicated rows outside the tile's window
   DBuf<uint32_t> tile_far_ptr;    // ntiles + 1 offsets into far_rows
+  // k_spmm_ring plan (spmm_ring.cuh); shares cv / far_rows / tile_far_ptr, cv.x = shared-memory byte offset
+  bool ring = false;
+  SpmmRing rg;
+  DBuf<uint4> ring_desc;          // per tile {first entry, end entry, first far row, end far row}
+  DBuf<int> ring_cta_ptr;         // nctas + 1 tile offsets: the contiguous tile range of every CTA
+  DBuf<long long> ring_clk;       // per-CTA cycles of a balancing launch
+  DBuf<unsigned char> ring_meta;  // per tile: {entries}, slice table, row order, diagonal (ring_meta_bytes(R) each)
+  DBuf<unsigned char> ring_blob;  // per tile: 16-bit shared-memory offsets then float weights, in consumption order
+  long long ring_entries = 0;     // sliced entries incl. padding
 };
 
 struct tcs_graph {

@@ -251,13 +251,13 @@ int tcs_impl_assemble(tcs_graph* g, int K) {
   S.n = (int)n;
   TRY(S.row_of.alloc(ctx, V));
   TRY(counts.alloc(ctx, (size_t)n + 1));
-  TRY(S.rowptr.alloc(ctx, (size_t)n + 1));
+  TRY(S.rowptr.alloc(ctx, (size_t)n + 1 + 8));  // + 8: the SpMM kernels copy 16-byte aligned slices
   LAUNCH(ctx, k_row_counts, div_up(V, 128), 128, 0, V, g->rowptr.p, g->col.p, isrow.p, row_scan.p, counts.p, S.row_of.p);
   TRY(tcs_impl_scan_u32(ctx, counts.p, S.rowptr.p, n));
   uint32_t nnz = 0;
   TRY(tcs_impl_read_u32(ctx, S.rowptr.p + n, &nnz));
   S.nnz_off = nnz;
-  TRY(S.col.alloc(ctx, nnz)); TRY(S.val.alloc(ctx, nnz)); TRY(S.diag.alloc(ctx, n));
+  TRY(S.col.alloc(ctx, nnz)); TRY(S.val.alloc(ctx, (size_t)nnz + 16)); TRY(S.diag.alloc(ctx, (size_t)n + 8));
   TRY(S.B.alloc(ctx, (size_t)n * S.Kp)); TRY(S.row_vertex.alloc(ctx, n));
   if (n) {
     CK(cudaMemsetAsync(S.B.p, 0, (size_t)n * S.Kp * 4, ctx->stream));

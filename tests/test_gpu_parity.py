@@ -176,3 +176,40 @@ def test_potentials_match_direct_solve(ctx, scenes):
     assert max(info.as_dict()["rel_residual"]) <= 1e-6
     assert np.abs(pg - po).max() < 5e-3   # ill-conditioned systems: residual 1e-6 does not bound the error by 1e-6
     assert np.count_nonzero(cg != co) <= 3
+
+
+@pytest.mark.parametrize("shape", [(640, 480, 7, 0.006), (1280, 960, 15, 0.005), (800, 600, 10, 0.006),
+                                   (800, 600, 18, 0.006)])
+def test_spmm_kernels_agree(ctx, shape, monkeypatch):
+    """The SpMM kernels (generic, tiled, ring pipeline in several shapes) are the same linear operator: applied to the
+    same random dense block their outputs agree to float32 summation-order noise, and the PCG solves built on them all
+    reach the 1e-6 residual with the same labels.  Label counts 8 / 16 / 11 / 19 = 2, 4, 3, 5 float4 lanes per row."""
+    from tcs_b200 import synth
+    w, h, nobj, res = shape
+    xyz, rgba, label = synth.make_scene(w, h, nobj, 7)
+    sx, sl, _ = seeds_from_labels(xyz, label, 0, 5)
+    ctx.upload_cloud(xyz, rgba)
+    out = {}
+    envs = (("generic", 1, {"TCS_SPMM": "v1"}), ("tiled", 2, {"TCS_SPMM": "tiled"}),
+            ("ring", 3, {"TCS_RING_MIN_TILES": "1"}),
+            ("ring_s2_nodup", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "2", "TCS_RING_DUP": "0", "TCS_RING_ROWS": "1024"}),
+            ("ring_s4_small", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "4", "TCS_RING_ROWS": "2048", "TCS_RING_FAR": "8",
+                                  "TCS_RING_DUP": "0"}))
+    for name, kid, env in envs:
+        for k in ("TCS_SPMM", "TCS_RING_MIN_TILES", "TCS_RING_S", "TCS_RING_DUP", "TCS_RING_ROWS", "TCS_RING_FAR"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        r = ctx.segment_cloud(res, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST)
+        info = r["info"].as_dict()
+        assert r["status"] == capi.OK and info["converged"] and max(info["rel_residual"]) <= 1e-6, name
+        g = r["graph"]
+        assert info["spmm_kernel"] == kid, (name, info["spmm_kernel"])
+        for seed in (1, 2):
+            diff, ref, dot, k = g.check_spmm(seed)
+            assert k == kid
+            assert diff <= 2e-5 * ref and dot < 1e-6, (name, diff, ref, dot)
+        out[name] = r["vertex_colour"].copy()
+        g.close()
+    for name in out:
+        assert np.count_nonzero(out[name] != out["generic"]) <= max(3, len(out[name]) // 1000), name
