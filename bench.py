@@ -267,6 +267,14 @@ def run_ours(args, rank, local_rank, world):
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         achieved = b_spmm / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        kname = {1: "k_spmm", 2: "k_spmm_tiled", 3: "k_spmm_ring"}.get(info.get("spmm_kernel"), "k_spmm")
+        traffic = None    # DRAM bytes per launch of that kernel from the committed ncu --set full capture
+        try:
+            tr = json.load(open(os.path.join(ROOT, "profiles", "spmm_traffic.json")))
+            if tr.get("kernel") == kname and not args.small:
+                traffic = int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])
+        except Exception:
+            pass
         out = {
             "metric": "rw_segmentation_vertices_per_s", "value": V_all / (ms_max * 1e-3), "unit": "vertices/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
@@ -278,8 +286,8 @@ def run_ours(args, rank, local_rank, world):
                     "d2h_bytes_per_step": 4 * n + 4 * int(Ve // args.steps), "ms_per_step": ms_e2e_max / args.steps},
             "gpu_launches": int(launches_all),
             "clocks": clocks,
-            "roofline": {"bound": "hbm", "kernel": "k_spmm (CG SpMM over all label columns)", "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": None,
+            "roofline": {"bound": "hbm", "kernel": kname + " (CG SpMM over all label columns)", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                          "algorithmic_bytes_per_launch": b_spmm, "avg_launch_ms": avg_ms,
                          "launches_per_step": spmm_n // args.steps, "spmm_share_of_step": spmm_ms / ms if ms else None,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650 GB/s"},
