@@ -133,6 +133,7 @@ struct tcs_system {
   DBuf<uint32_t> tile_far_ptr;    // ntiles + 1 offsets into far_rows
   // k_spmm_ring plan (spmm_ring.cuh); shares cv / far_rows / tile_far_ptr, cv.x = shared-memory byte offset
   bool ring = false;
+  bool plan_stale = false;        // the last solve ended on a compacted column set: hooks re-plan at full width
   SpmmRing rg;
   DBuf<uint4> ring_desc;          // per tile {first entry, end entry, first far row, end far row}
   DBuf<int> ring_cta_ptr;         // nctas + 1 tile offsets: the contiguous tile range of every CTA

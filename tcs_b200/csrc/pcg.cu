@@ -92,7 +92,8 @@ __global__ void __launch_bounds__(256) k_spmm(int n, int Q, const uint32_t* __re
 __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __restrict__ B,
                                                   const float* __restrict__ diag, float* __restrict__ invd,
                                                   float4* __restrict__ R, float4* __restrict__ P, double* __restrict__ X,
-                                                  double* __restrict__ rz, double* __restrict__ bb) {
+                                                  float4* __restrict__ Xd, double* __restrict__ rz,
+                                                  double* __restrict__ bb) {
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -109,6 +110,7 @@ __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __
       double2* x = (double2*)(X + 4 * i);
       x[0] = make_double2(0.0, 0.0);
       x[1] = make_double2(0.0, 0.0);
+      Xd[i] = make_float4(0.f, 0.f, 0.f, 0.f);
       const double di = (double)inv;
       a_bb[0] += (double)b.x * b.x; a_bb[1] += (double)b.y * b.y; a_bb[2] += (double)b.z * b.z; a_bb[3] += (double)b.w * b.w;
       a_rz[0] += (double)b.x * b.x * di; a_rz[1] += (double)b.y * b.y * di;
@@ -120,13 +122,18 @@ __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __
   reduce_columns(a_bb, q, Q, active, sm, bb);
 }
 
-// alpha = rz / pAp ; x += alpha p (float64: an fp32 x stalls the true residual at 1e-4) ;
-// r -= alpha Ap ; rz_next += r . D^-1 r
+// alpha = rz / pAp ; xd += alpha p ; r -= alpha Ap ; rz_next += r . D^-1 r
+// x is carried as a float64 base X plus a float32 increment xd that k_flush_x folds into X before every float64
+// true-residual evaluation (an fp32 x alone stalls the true residual at 1e-4; the increment of
+// `check_every` iterations is small next to x, so its float32 rounding is far below the tolerance) - 8 instead of
+// 16 bytes of x traffic per element and iteration.
 __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* __restrict__ P,
                                                     const float4* __restrict__ AP, float4* __restrict__ R,
-                                                    double* __restrict__ X, const float* __restrict__ invd,
+                                                    float4* __restrict__ Xd, const float* __restrict__ invd,
                                                     const double* __restrict__ rz, const double* __restrict__ pAp,
-                                                    double* __restrict__ rz_next, const int* __restrict__ frozen) {
+                                                    double* __restrict__ rz_next, const int* __restrict__ frozen,
+                                                    const double* __restrict__ rz0, double done_factor,
+                                                    const double* __restrict__ pr) {
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -134,13 +141,16 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
   double acc[4] = {0, 0, 0, 0};
   if (active) {
     float al[4];
-    double ald[4];
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      double den = pAp[4 * q + j], num = rz[4 * q + j];
-      // a column that reached the tolerance is frozen: iterating on it further only amplifies rounding noise
-      ald[j] = (den > 0.0 && num > 0.0 && !frozen[4 * q + j]) ? num / den : 0.0;
-      al[j] = (float)ald[j];
+      // pr != NULL on the iteration after a residual replacement: exact line search along p (see k_true_residual)
+      const double den = pAp[4 * q + j], num = pr ? pr[4 * q + j] : rz[4 * q + j];
+      // A column that reached the tolerance is frozen (host flag), and so is one whose recurrence residual fell far
+      // below it between two checks (rz <= done_factor * rz_initial): iterating on it further only amplifies rounding
+      // noise, and once r underflows in float32 rz / pAp is no longer a step length.
+      const bool live = den > 0.0 && num > done_factor * rz0[4 * q + j] && !frozen[4 * q + j];
+      const double ratio = live ? num / den : 0.0;
+      al[j] = ratio < 1e30 ? (float)ratio : 0.0f;
     }
     const int stride = gridDim.x * rows_per_block;
     int row = blockIdx.x * rows_per_block + local;
@@ -148,16 +158,14 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
     for (; row + stride < n; row += 2 * stride) {
       const size_t i0 = (size_t)row * Q + q, i1 = (size_t)(row + stride) * Q + q;
       const float4 p0 = P[i0], p1 = P[i1], ap0 = AP[i0], ap1 = AP[i1];
-      float4 r0 = R[i0], r1 = R[i1];
-      double2* xp0 = (double2*)(X + 4 * i0);
-      double2* xp1 = (double2*)(X + 4 * i1);
-      double2 x0a = xp0[0], x0b = xp0[1], x1a = xp1[0], x1b = xp1[1];
+      float4 r0 = R[i0], r1 = R[i1], x0 = Xd[i0], x1 = Xd[i1];
       const float d0 = invd[row], d1 = invd[row + stride];
-      x0a.x += ald[0] * (double)p0.x; x0a.y += ald[1] * (double)p0.y; x0b.x += ald[2] * (double)p0.z; x0b.y += ald[3] * (double)p0.w;
-      x1a.x += ald[0] * (double)p1.x; x1a.y += ald[1] * (double)p1.y; x1b.x += ald[2] * (double)p1.z; x1b.y += ald[3] * (double)p1.w;
-      r0.x -= al[0] * ap0.x; r0.y -= al[1] * ap0.y; r0.z -= al[2] * ap0.z; r0.w -= al[3] * ap0.w;
-      r1.x -= al[0] * ap1.x; r1.y -= al[1] * ap1.y; r1.z -= al[2] * ap1.z; r1.w -= al[3] * ap1.w;
-      xp0[0] = x0a; xp0[1] = x0b; xp1[0] = x1a; xp1[1] = x1b; R[i0] = r0; R[i1] = r1;
+      // a dead column (alpha = 0) is left untouched: its p / Ap may hold inf or nan after float32 underflow
+      if (al[0] != 0.f) { x0.x += al[0] * p0.x; x1.x += al[0] * p1.x; r0.x -= al[0] * ap0.x; r1.x -= al[0] * ap1.x; }
+      if (al[1] != 0.f) { x0.y += al[1] * p0.y; x1.y += al[1] * p1.y; r0.y -= al[1] * ap0.y; r1.y -= al[1] * ap1.y; }
+      if (al[2] != 0.f) { x0.z += al[2] * p0.z; x1.z += al[2] * p1.z; r0.z -= al[2] * ap0.z; r1.z -= al[2] * ap1.z; }
+      if (al[3] != 0.f) { x0.w += al[3] * p0.w; x1.w += al[3] * p1.w; r0.w -= al[3] * ap0.w; r1.w -= al[3] * ap1.w; }
+      Xd[i0] = x0; Xd[i1] = x1; R[i0] = r0; R[i1] = r1;
       // float64 products: r can sit far below sqrt(FLT_MIN) on quickly converging columns
       const double e0 = (double)d0, e1 = (double)d1;
       acc[0] += (double)r0.x * (double)r0.x * e0 + (double)r1.x * (double)r1.x * e1;
@@ -168,13 +176,13 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
     for (; row < n; row += stride) {
       const size_t i = (size_t)row * Q + q;
       const float4 p = P[i], ap = AP[i];
-      float4 r = R[i];
-      double2* xp = (double2*)(X + 4 * i);
-      double2 xa = xp[0], xb = xp[1];
+      float4 r = R[i], x = Xd[i];
       const float d = invd[row];
-      xa.x += ald[0] * (double)p.x; xa.y += ald[1] * (double)p.y; xb.x += ald[2] * (double)p.z; xb.y += ald[3] * (double)p.w;
-      r.x -= al[0] * ap.x; r.y -= al[1] * ap.y; r.z -= al[2] * ap.z; r.w -= al[3] * ap.w;
-      xp[0] = xa; xp[1] = xb; R[i] = r;
+      if (al[0] != 0.f) { x.x += al[0] * p.x; r.x -= al[0] * ap.x; }
+      if (al[1] != 0.f) { x.y += al[1] * p.y; r.y -= al[1] * ap.y; }
+      if (al[2] != 0.f) { x.z += al[2] * p.z; r.z -= al[2] * ap.z; }
+      if (al[3] != 0.f) { x.w += al[3] * p.w; r.w -= al[3] * ap.w; }
+      Xd[i] = x; R[i] = r;
       const double e = (double)d;
       acc[0] += (double)r.x * (double)r.x * e; acc[1] += (double)r.y * (double)r.y * e;
       acc[2] += (double)r.z * (double)r.z * e; acc[3] += (double)r.w * (double)r.w * e;
@@ -183,11 +191,41 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
   reduce_columns(acc, q, Q, active, sm, rz_next);
 }
 
+// X += xd ; xd = 0  (before every float64 true residual)
+__global__ void k_flush_x(size_t count, double* __restrict__ X, float* __restrict__ Xd) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  X[i] += (double)Xd[i];
+  Xd[i] = 0.f;
+}
+
+// column compaction: out[row, k] = in[row, src[k]] (0 where src[k] < 0); Kin / Kout are the row widths
+template <typename T>
+__global__ void k_repack_columns(size_t n, int Kin, int Kout, const int* __restrict__ src, const T* __restrict__ in,
+                                 T* __restrict__ out) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n * Kout) return;
+  const size_t row = i / Kout;
+  const int k = (int)(i - row * Kout), sk = src[k];
+  out[i] = sk >= 0 ? in[row * Kin + sk] : (T)0;
+}
+// X_full[row, dst[k]] = X_work[row, k] for the working columns with dst[k] >= 0
+__global__ void k_scatter_columns(size_t n, int Kw, int Kfull, const int* __restrict__ dst, const double* __restrict__ Xw,
+                                  double* __restrict__ Xfull) {
+  const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (i >= n * Kw) return;
+  const size_t row = i / Kw;
+  const int dk = dst[(int)(i - row * Kw)];
+  if (dk >= 0) Xfull[row * Kfull + dk] = Xw[i];
+}
+
 // beta = rz_next / rz ; p = D^-1 r + beta p ; block 0 clears the accumulators of the coming iterations
 __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __restrict__ R, float4* __restrict__ P,
                                                  const float* __restrict__ invd, const double* __restrict__ rz,
                                                  const double* __restrict__ rz_next, double* __restrict__ clear_a,
-                                                 double* __restrict__ clear_b, const int* __restrict__ frozen) {
+                                                 double* __restrict__ clear_b, const int* __restrict__ frozen,
+                                                 const double* __restrict__ rz0, double done_factor,
+                                                 const double* __restrict__ pr) {
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
   if (blockIdx.x == 0)
@@ -196,8 +234,11 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
   float be[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
-    double den = rz[4 * q + j], num = rz_next[4 * q + j];
-    be[j] = (den > 0.0 && !frozen[4 * q + j]) ? (float)(num / den) : 0.0f;
+    const double den = rz[4 * q + j], num = rz_next[4 * q + j];
+    // after a replacement whose p is not even a descent direction for the new r (p.r <= 0): restart from z
+    const bool live = den > done_factor * rz0[4 * q + j] && den > 0.0 && !frozen[4 * q + j] && !(pr && pr[4 * q + j] <= 0.0);
+    const double ratio = live ? num / den : 0.0;
+    be[j] = ratio < 1e30 ? (float)ratio : 0.0f;
   }
   const int stride = gridDim.x * rows_per_block;
   int row = blockIdx.x * rows_per_block + local;
@@ -206,10 +247,11 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
     const float4 r0 = R[i0], r1 = R[i1];
     float4 p0 = P[i0], p1 = P[i1];
     const float d0 = invd[row], d1 = invd[row + stride];
-    p0.x = r0.x * d0 + be[0] * p0.x; p0.y = r0.y * d0 + be[1] * p0.y;
-    p0.z = r0.z * d0 + be[2] * p0.z; p0.w = r0.w * d0 + be[3] * p0.w;
-    p1.x = r1.x * d1 + be[0] * p1.x; p1.y = r1.y * d1 + be[1] * p1.y;
-    p1.z = r1.z * d1 + be[2] * p1.z; p1.w = r1.w * d1 + be[3] * p1.w;
+    // beta == 0 restarts the direction without reading the old p (which may hold inf / nan on a dead column)
+    p0.x = r0.x * d0 + (be[0] != 0.f ? be[0] * p0.x : 0.f); p0.y = r0.y * d0 + (be[1] != 0.f ? be[1] * p0.y : 0.f);
+    p0.z = r0.z * d0 + (be[2] != 0.f ? be[2] * p0.z : 0.f); p0.w = r0.w * d0 + (be[3] != 0.f ? be[3] * p0.w : 0.f);
+    p1.x = r1.x * d1 + (be[0] != 0.f ? be[0] * p1.x : 0.f); p1.y = r1.y * d1 + (be[1] != 0.f ? be[1] * p1.y : 0.f);
+    p1.z = r1.z * d1 + (be[2] != 0.f ? be[2] * p1.z : 0.f); p1.w = r1.w * d1 + (be[3] != 0.f ? be[3] * p1.w : 0.f);
     P[i0] = p0; P[i1] = p1;
   }
   for (; row < n; row += stride) {
@@ -217,23 +259,28 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
     const float4 r = R[i];
     float4 p = P[i];
     const float d = invd[row];
-    p.x = r.x * d + be[0] * p.x; p.y = r.y * d + be[1] * p.y;
-    p.z = r.z * d + be[2] * p.z; p.w = r.w * d + be[3] * p.w;
+    p.x = r.x * d + (be[0] != 0.f ? be[0] * p.x : 0.f); p.y = r.y * d + (be[1] != 0.f ? be[1] * p.y : 0.f);
+    p.z = r.z * d + (be[2] != 0.f ? be[2] * p.z : 0.f); p.w = r.w * d + (be[3] != 0.f ? be[3] * p.w : 0.f);
     P[i] = p;
   }
 }
 
-// float64 true residual r = b - L x (replaces the recurrence residual), rr = ||r||^2, rz = r . D^-1 r
+// float64 true residual r = b - L x (replaces the recurrence residual), rr = ||r||^2, rz = r . D^-1 r, pr = p . r.
+// The replaced r is not the vector the current direction p was built for (it differs by the rounding the recurrence
+// and the float32 x increments accumulated), so the step after a replacement uses the exact line search
+// alpha = p.r / p.Ap instead of r.z / p.Ap: with r.z the step overshoots by (|r_true| / |r_recurrence|)^2 and a
+// column that is almost converged diverges.
 __global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint32_t* __restrict__ rowptr,
                                                        const int* __restrict__ col, const float* __restrict__ val,
                                                        const float* __restrict__ diag, const float4* __restrict__ B,
-                                                       const double* __restrict__ X, float4* __restrict__ R,
-                                                       double* __restrict__ rr, double* __restrict__ rz) {
+                                                       const double* __restrict__ X, const float4* __restrict__ P,
+                                                       float4* __restrict__ R, double* __restrict__ rr,
+                                                       double* __restrict__ rz, double* __restrict__ pr) {
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
   const bool active = local < rows_per_block;
-  double a_rr[4] = {0, 0, 0, 0}, a_rz[4] = {0, 0, 0, 0};
+  double a_rr[4] = {0, 0, 0, 0}, a_rz[4] = {0, 0, 0, 0}, a_pr[4] = {0, 0, 0, 0};
   if (active) {
     for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
       const size_t i = (size_t)row * Q + q;
@@ -256,11 +303,16 @@ __global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint3
       for (int j = 0; j < 4; ++j) a_rr[j] += r[j] * r[j];
       a_rz[0] += (double)rf.x * rf.x * di; a_rz[1] += (double)rf.y * rf.y * di;
       a_rz[2] += (double)rf.z * rf.z * di; a_rz[3] += (double)rf.w * rf.w * di;
+      const float4 pv = P[i];
+      a_pr[0] += (double)pv.x * rf.x; a_pr[1] += (double)pv.y * rf.y;
+      a_pr[2] += (double)pv.z * rf.z; a_pr[3] += (double)pv.w * rf.w;
     }
   }
   reduce_columns(a_rr, q, Q, active, sm, rr);
   __syncthreads();
   reduce_columns(a_rz, q, Q, active, sm, rz);
+  __syncthreads();
+  reduce_columns(a_pr, q, Q, active, sm, pr);
 }
 
 // assignColors (impl/random_walker.hpp:209-222): first maximal potential of the row; rows whose potentials are all
@@ -330,6 +382,7 @@ int spmm_plan_ring(tcs_ctx* ctx, tcs_system& S);
 int spmm_plan(tcs_ctx* ctx, tcs_system& S) {
   S.tiled = false;
   S.ring = false;
+  S.plan_stale = false;
   const char* force = getenv("TCS_SPMM");
   if (force && !strcmp(force, "v1")) return TCS_OK;
   if (!(force && !strcmp(force, "tiled"))) {
@@ -648,87 +701,178 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     g->pot_K = 0;
   }
 
-  int iterations = 0, converged = 1;
+  int iterations = 0, converged = 1, kernel_at_start = 0;
   double rel[TCS_MAX_LABELS] = {0};
   float spmm_sum_ms = 0.f;
   int spmm_timed = 0, spmm_launches = 0;
   if (n > 0) {
-    const size_t nk = (size_t)n * Kp;
-    TRY(S.X.alloc(ctx, nk)); TRY(S.P.alloc(ctx, nk)); TRY(S.R.alloc(ctx, nk)); TRY(S.AP.alloc(ctx, nk));
+    // Working set: the label columns still iterating, packed to a multiple of 4.  wmap[kw] = original column of working
+    // column kw (-1 = padding).  Columns are independent systems (one right-hand side each): when enough of them
+    // have reached the tolerance to drop a float4 of columns, the survivors are re-packed and the SpMM re-planned
+    // for the narrower rows, so converged columns stop costing bandwidth (C4: 6 of 16 columns finish within 700 of
+    // 8050 iterations).  TCS_COMPACT=0 keeps all columns (they are then frozen instead).
+    const int Kp0 = Kp;
+    int Kw = Kp0, Qw = Q;
+    std::vector<int> wmap(Kw);
+    for (int k = 0; k < Kw; ++k) wmap[k] = k < K ? k : -1;
+    std::vector<char> done(K, 0);
+    const bool compact_enabled = env_int("TCS_COMPACT", 1) != 0;
+    bool compacted = false;
+    const size_t nk = (size_t)n * Kp0;
+    DBuf<double> Xw;   // float64 solution of the working columns (becomes S.X when no compaction happens)
+    DBuf<float> Xd;    // float32 increment since the last flush
+    DBuf<float> Bw;    // right-hand sides of the working columns (S.B itself until the first compaction)
+    S.X.release();
+    TRY(Xw.alloc(ctx, nk)); TRY(Xd.alloc(ctx, nk));
+    TRY(S.P.alloc(ctx, nk)); TRY(S.R.alloc(ctx, nk)); TRY(S.AP.alloc(ctx, nk));
     DBuf<float> invd;
     TRY(invd.alloc(ctx, n));
-    // scalar accumulators: pAp[3][Kp], rz[3][Kp], rr[Kp], bb[Kp]
+    // scalar accumulators, row stride Kp0: pAp[3], rz[3], rr, bb, rz of the initial residual
+    const int kScalRows = 10;
     DBuf<double> scal;
-    TRY(scal.alloc(ctx, (size_t)8 * Kp));
-    CK(cudaMemsetAsync(scal.p, 0, (size_t)8 * Kp * 8, ctx->stream));
+    TRY(scal.alloc(ctx, (size_t)kScalRows * Kp0));
+    CK(cudaMemsetAsync(scal.p, 0, (size_t)kScalRows * Kp0 * 8, ctx->stream));
     double* d_pAp = scal.p;
-    double* d_rz = scal.p + 3 * Kp;
-    double* d_rr = scal.p + 6 * Kp;
-    double* d_bb = scal.p + 7 * Kp;
-    DBuf<int> frozen;
-    TRY(frozen.alloc(ctx, Kp));
-    CK(cudaMemsetAsync(frozen.p, 0, (size_t)Kp * 4, ctx->stream));
+    double* d_rz = scal.p + 3 * Kp0;
+    double* d_rr = scal.p + 6 * Kp0;
+    double* d_bb = scal.p + 7 * Kp0;
+    double* d_rz0 = scal.p + 8 * Kp0;
+    double* d_pr = scal.p + 9 * Kp0;   // p . r of the last residual replacement
+    // device-side "done": recurrence residual four decades below the tolerance (in the D^-1 norm, relative to b) -
+    // far from the tolerance itself (the two norms differ), far above float32 underflow of r
+    const double done_factor = 1e-8 * opts.tolerance * opts.tolerance;
+    DBuf<int> frozen, d_cols;
+    TRY(frozen.alloc(ctx, Kp0)); TRY(d_cols.alloc(ctx, 2 * (size_t)Kp0));
+    CK(cudaMemsetAsync(frozen.p, 0, (size_t)Kp0 * 4, ctx->stream));
     int* h_frozen = (int*)((char*)ctx->h_pin + 2048);
-    for (int k = 0; k < Kp; ++k) h_frozen[k] = 0;
-    const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
+    for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
+    PcgLaunch L = pcg_launch_shape(ctx, n, Qw);
     TRY(spmm_plan(ctx, S));
+    kernel_at_start = S.ring ? 3 : S.tiled ? 2 : 1;
     const float4* B4 = (const float4*)S.B.p;
     float4* P4 = (float4*)S.P.p;
     float4* R4 = (float4*)S.R.p;
     float4* AP4 = (float4*)S.AP.p;
-    LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Q, B4, S.diag.p, invd.p, R4, P4, S.X.p, d_rz, d_bb);
-    std::vector<double> h(2 * Kp);
-    // sampled SpMM timing: one event pair every `stride` launches
+    LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Qw, B4, S.diag.p, invd.p, R4, P4, Xw.p, (float4*)Xd.p, d_rz, d_bb);
+    CK(cudaMemcpyAsync(d_rz0, d_rz, (size_t)Kp0 * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    std::vector<double> h((size_t)kScalRows * Kp0);
+    // sampled SpMM timing: one event pair per launch for the first launches (full width)
     const int kMaxSamples = 64;
     std::vector<cudaEvent_t> evs;
     if (opts.time_spmm) {
       evs.resize(2 * kMaxSamples);
       for (auto& e : evs) CK(cudaEventCreate(&e));
     }
-    int sample_stride = 1, samples = 0;
+    int samples = 0;
     converged = 0;
     int it = 0;
     while (it < opts.max_iterations) {
       const int chunk = std::min(opts.check_every, opts.max_iterations - it);
       for (int j = 0; j < chunk; ++j, ++it) {
         const int s0 = it % 3, s1 = (it + 1) % 3, s2 = (it + 2) % 3;
-        const bool timed = opts.time_spmm && samples < kMaxSamples && (spmm_launches % sample_stride) == 0;
+        const double* pr = (j == 0 && it > 0) ? d_pr : nullptr;  // first step after a residual replacement
+        const bool timed = opts.time_spmm && samples < kMaxSamples && !compacted;
         if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
-        launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp);
-        ctx->launches += 0;
+        launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp0);
         if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
         ++spmm_launches;
-        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Q, P4, AP4, R4, S.X.p, invd.p, d_rz + s0 * Kp,
-               d_pAp + s0 * Kp, d_rz + s1 * Kp, frozen.p);
-        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Q, R4, P4, invd.p, d_rz + s0 * Kp, d_rz + s1 * Kp,
-               d_pAp + s1 * Kp, d_rz + s2 * Kp, frozen.p);
+        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Qw, P4, AP4, R4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
+               d_pAp + s0 * Kp0, d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr);
+        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Qw, R4, P4, invd.p, d_rz + s0 * Kp0, d_rz + s1 * Kp0,
+               d_pAp + s1 * Kp0, d_rz + s2 * Kp0, frozen.p, d_rz0, done_factor, pr);
       }
-      if (opts.time_spmm && samples == kMaxSamples && sample_stride == 1) {
-        // keep the first samples; later launches are not timed (the kernel's duration does not depend on `it`)
-        sample_stride = 1 << 30;
-      }
-      // float64 true residual replaces the recurrence residual; rz of the coming iteration is recomputed from it
-      CK(cudaMemsetAsync(d_rr, 0, (size_t)Kp * 8, ctx->stream));
-      CK(cudaMemsetAsync(d_rz + (it % 3) * Kp, 0, (size_t)Kp * 8, ctx->stream));
-      LAUNCH(ctx, k_true_residual, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.diag.p, B4, S.X.p, R4,
-             d_rr, d_rz + (it % 3) * Kp);
-      CK(cudaMemcpyAsync(ctx->h_pin, d_rr, (size_t)2 * Kp * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      // fold the float32 increment into the float64 solution; the float64 true residual replaces the recurrence
+      // residual, and rz of the coming iteration is recomputed from it
+      const size_t nkw = (size_t)n * Kw;
+      LAUNCH(ctx, k_flush_x, div_up(nkw, 256), 256, 0, nkw, Xw.p, Xd.p);
+      CK(cudaMemsetAsync(d_rr, 0, (size_t)Kp0 * 8, ctx->stream));
+      CK(cudaMemsetAsync(d_rz + (it % 3) * Kp0, 0, (size_t)Kp0 * 8, ctx->stream));
+      CK(cudaMemsetAsync(d_pr, 0, (size_t)Kp0 * 8, ctx->stream));
+      LAUNCH(ctx, k_true_residual, L.grid, L.block, L.smem, n, Qw, S.rowptr.p, S.col.p, S.val.p, S.diag.p, B4, Xw.p, P4, R4,
+             d_rr, d_rz + (it % 3) * Kp0, d_pr);
+      CK(cudaMemcpyAsync(ctx->h_pin, d_rr, (size_t)2 * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
       CK(cudaStreamSynchronize(ctx->stream));
-      memcpy(h.data(), ctx->h_pin, (size_t)2 * Kp * 8);
-      bool all = true;
-      for (int k = 0; k < K; ++k) {
-        double rr = h[k], bb = h[Kp + k];
+      memcpy(h.data(), ctx->h_pin, (size_t)2 * Kp0 * 8);
+      int active_cols = 0;
+      for (int kw = 0; kw < Kw; ++kw) {
+        const int k = wmap[kw];
+        if (k < 0) continue;
+        const double rr = h[kw], bb = h[Kp0 + kw];
         rel[k] = bb > 0.0 ? std::sqrt(rr / bb) : 0.0;
-        if (!(rel[k] <= opts.tolerance)) all = false;
-        else h_frozen[k] = 1;
+        if (rel[k] <= opts.tolerance) { done[k] = 1; h_frozen[kw] = 1; }
+        if (!done[k]) ++active_cols;
       }
-      if (!all) CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp * 4, cudaMemcpyHostToDevice, ctx->stream));
       if (getenv("TCS_DEBUG")) {
         fprintf(stderr, "[tcs] it=%d rel:", it);
         for (int k = 0; k < K; ++k) fprintf(stderr, " %.2e", rel[k]);
         fprintf(stderr, "\n");
       }
-      if (all) { converged = 1; break; }
+      if (active_cols == 0) { converged = 1; break; }
+      const int newKw = std::max(4, (active_cols + 3) & ~3);
+      if (compact_enabled && newKw < Kw && it < opts.max_iterations) {
+        // ---- drop the converged columns
+        if (!S.X.p) {
+          TRY(S.X.alloc(ctx, nk));
+          CK(cudaMemsetAsync(S.X.p, 0, nk * 8, ctx->stream));
+        }
+        std::vector<int> cols(2 * (size_t)Kp0, -1), newmap;  // [0, Kp0): scatter targets; [Kp0, 2 Kp0): repack sources
+        for (int kw = 0; kw < Kw; ++kw) {
+          cols[kw] = wmap[kw];
+          if (wmap[kw] >= 0 && !done[wmap[kw]]) { cols[Kp0 + newmap.size()] = kw; newmap.push_back(wmap[kw]); }
+        }
+        newmap.resize(newKw, -1);
+        CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+        LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
+        const size_t nk2 = (size_t)n * newKw;
+        DBuf<float> P2, R2, B2, Xd2, AP2;
+        DBuf<double> X2;
+        TRY(P2.alloc(ctx, nk2)); TRY(R2.alloc(ctx, nk2)); TRY(B2.alloc(ctx, nk2)); TRY(Xd2.alloc(ctx, nk2));
+        TRY(AP2.alloc(ctx, nk2)); TRY(X2.alloc(ctx, nk2));
+        const int* src = d_cols.p + Kp0;
+        LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.P.p, P2.p);
+        LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.R.p, R2.p);
+        LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src,
+               Bw.p ? Bw.p : S.B.p, B2.p);
+        LAUNCH(ctx, k_repack_columns<double>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, Xw.p, X2.p);
+        CK(cudaMemsetAsync(Xd2.p, 0, nk2 * 4, ctx->stream));
+        // per-column scalars: same permutation on the host (we are at a synchronisation point anyway)
+        CK(cudaMemcpyAsync(h.data(), scal.p, (size_t)kScalRows * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));  // also: `cols` was read by the copy above
+        std::vector<double> h2((size_t)kScalRows * Kp0, 0.0);
+        for (int r8 = 0; r8 < kScalRows; ++r8)
+          for (int k2 = 0; k2 < newKw; ++k2)
+            if (cols[Kp0 + k2] >= 0) h2[(size_t)r8 * Kp0 + k2] = h[(size_t)r8 * Kp0 + cols[Kp0 + k2]];
+        CK(cudaMemcpyAsync(scal.p, h2.data(), (size_t)kScalRows * Kp0 * 8, cudaMemcpyHostToDevice, ctx->stream));
+        for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
+        CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));  // h2 is a local vector
+        S.P.swap(P2); S.R.swap(R2); S.AP.swap(AP2); Bw.swap(B2); Xw.swap(X2); Xd.swap(Xd2);
+        Kw = newKw; Qw = Kw / 4; wmap = newmap;
+        S.Kp = Kw;
+        compacted = true;
+        L = pcg_launch_shape(ctx, n, Qw);
+        TRY(spmm_plan(ctx, S));
+        B4 = (const float4*)Bw.p; P4 = (float4*)S.P.p; R4 = (float4*)S.R.p; AP4 = (float4*)S.AP.p;
+        if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] it=%d: %d columns left, working width %d\n", it, active_cols, Kw);
+      } else {
+        CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+      }
+    }
+    // the float64 solution of all columns, n x Kp0
+    if (!compacted) {
+      S.X.swap(Xw);
+    } else {
+      std::vector<int> cols(2 * (size_t)Kp0, -1);
+      for (int kw = 0; kw < Kw; ++kw) cols[kw] = wmap[kw];
+      CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+      const size_t nkw = (size_t)n * Kw;
+      LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
+      CK(cudaStreamSynchronize(ctx->stream));
+      // the SpMM plan and P belong to the narrow working set: the measurement hooks re-plan at full width
+      S.Kp = Kp0;
+      S.ring = S.tiled = false;
+      S.plan_stale = true;
+      S.P.release();
     }
     iterations = it;
     CK(cudaEventRecord(e_solve1, ctx->stream));
@@ -761,7 +905,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     info->converged = converged;
     for (int k = 0; k < K; ++k) info->rel_residual[k] = rel[k];
     info->spmm_launches = spmm_launches;
-    info->spmm_kernel = g->sys.n == 0 ? 0 : g->sys.ring ? 3 : g->sys.tiled ? 2 : 1;
+    info->spmm_kernel = kernel_at_start;  // the kernel planned for the full label block
     info->spmm_ms = spmm_timed ? spmm_sum_ms / spmm_timed * spmm_launches : 0.f;
   }
   CK(cudaGetLastError());
@@ -791,13 +935,27 @@ extern "C" int tcs_random_walker(tcs_graph* g, uint32_t* colours, int ncolours, 
   return st;
 }
 
+namespace {
+// the measurement hooks work on the full label block: after a solve that ended on a compacted column set, allocate
+// a full-width P again and plan the SpMM for it
+int ensure_full_plan(tcs_ctx* ctx, tcs_system& S) {
+  if (!S.plan_stale) return TCS_OK;
+  const size_t nk = (size_t)S.n * S.Kp;
+  TRY(S.P.alloc(ctx, nk)); TRY(S.AP.alloc(ctx, nk));
+  CK(cudaMemsetAsync(S.P.p, 0, nk * 4, ctx->stream));
+  TRY(spmm_plan(ctx, S));
+  return TCS_OK;
+}
+}  // namespace
+
 // bench hook: the SpMM alone on the system of the last solve, `reps` launches between two events
 extern "C" int tcs_bench_spmm(tcs_graph* g, int reps, float* avg_ms, long long* algorithmic_bytes) {
   if (!g || reps < 1) return TCS_ERR_INPUT;
   tcs_ctx* ctx = g->ctx;
   tcs_system& S = g->sys;
-  if (S.n == 0 || !S.P.p) return tcs_fail(ctx, TCS_ERR_STATE, "no assembled system (run the random walker first)");
+  if (S.n == 0 || (!S.P.p && !S.plan_stale)) return tcs_fail(ctx, TCS_ERR_STATE, "no assembled system (run the random walker first)");
   CK(cudaSetDevice(ctx->device));
+  TRY(ensure_full_plan(ctx, S));
   const int n = S.n, Kp = S.Kp, Q = Kp / 4;
   TRY(S.AP.alloc(ctx, (size_t)n * Kp));
   DBuf<double> acc;
@@ -844,8 +1002,9 @@ extern "C" int tcs_check_spmm(tcs_graph* g, unsigned seed, double* max_abs_diff,
   if (!g) return TCS_ERR_INPUT;
   tcs_ctx* ctx = g->ctx;
   tcs_system& S = g->sys;
-  if (S.n == 0 || !S.P.p) return tcs_fail(ctx, TCS_ERR_STATE, "no assembled system (run the random walker first)");
+  if (S.n == 0 || (!S.P.p && !S.plan_stale)) return tcs_fail(ctx, TCS_ERR_STATE, "no assembled system (run the random walker first)");
   CK(cudaSetDevice(ctx->device));
+  TRY(ensure_full_plan(ctx, S));
   const int n = S.n, Kp = S.Kp, Q = Kp / 4;
   const size_t nk = (size_t)n * Kp;
   DBuf<float> ap1, ap2;
