@@ -10,6 +10,7 @@
 #include <cmath>
 #include <algorithm>
 #include <cstdlib>
+#include <chrono>
 
 #include "common.cuh"
 
@@ -122,18 +123,25 @@ __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __
   reduce_columns(a_bb, q, Q, active, sm, bb);
 }
 
-// alpha = rz / pAp ; xd += alpha p ; r -= alpha Ap ; rz_next += r . D^-1 r
-// x is carried as a float64 base X plus a float32 increment xd that k_flush_x folds into X before every float64
-// true-residual evaluation (an fp32 x alone stalls the true residual at 1e-4, SURVEY.md H5; the increment of
-// `check_every` iterations is small next to x, so its float32 rounding is far below the tolerance) - 8 instead of
-// 16 bytes of x traffic per element and iteration.
-__global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* __restrict__ P,
-                                                    const float4* __restrict__ AP, float4* __restrict__ R,
-                                                    float4* __restrict__ Xd, const float* __restrict__ invd,
-                                                    const double* __restrict__ rz, const double* __restrict__ pAp,
-                                                    double* __restrict__ rz_next, const int* __restrict__ frozen,
-                                                    const double* __restrict__ rz0, double done_factor,
-                                                    const double* __restrict__ pr) {
+// Step length of column c: alpha = r.z / p.Ap, or the exact line search p.r / p.Ap on the iteration after a residual
+// replacement (pr != NULL, see k_true_residual).  A column that reached the tolerance is frozen (host flag), and so
+// is one whose recurrence residual fell far below it between two checks (rz <= done_factor * rz_initial): iterating
+// on it further only amplifies rounding noise, and once r underflows in float32 rz / pAp is no longer a step length.
+__device__ __forceinline__ float pcg_alpha(int c, const double* __restrict__ rz, const double* __restrict__ pAp,
+                                           const int* __restrict__ frozen, const double* __restrict__ rz0,
+                                           double done_factor, const double* __restrict__ pr) {
+  const double den = pAp[c], num = pr ? pr[c] : rz[c];
+  const bool live = den > 0.0 && num > done_factor * rz0[c] && !frozen[c];
+  const double ratio = live ? num / den : 0.0;
+  return ratio < 1e30 ? (float)ratio : 0.0f;
+}
+
+// r -= alpha Ap ; rz_next += r . D^-1 r     (x += alpha p happens in k_pcg_dir, which reads p anyway)
+__global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* __restrict__ AP, float4* __restrict__ R,
+                                                    const float* __restrict__ invd, const double* __restrict__ rz,
+                                                    const double* __restrict__ pAp, double* __restrict__ rz_next,
+                                                    const int* __restrict__ frozen, const double* __restrict__ rz0,
+                                                    double done_factor, const double* __restrict__ pr) {
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -142,47 +150,42 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
   if (active) {
     float al[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      // pr != NULL on the iteration after a residual replacement: exact line search along p (see k_true_residual)
-      const double den = pAp[4 * q + j], num = pr ? pr[4 * q + j] : rz[4 * q + j];
-      // A column that reached the tolerance is frozen (host flag), and so is one whose recurrence residual fell far
-      // below it between two checks (rz <= done_factor * rz_initial): iterating on it further only amplifies rounding
-      // noise, and once r underflows in float32 rz / pAp is no longer a step length.
-      const bool live = den > 0.0 && num > done_factor * rz0[4 * q + j] && !frozen[4 * q + j];
-      const double ratio = live ? num / den : 0.0;
-      al[j] = ratio < 1e30 ? (float)ratio : 0.0f;
-    }
+    for (int j = 0; j < 4; ++j) al[j] = pcg_alpha(4 * q + j, rz, pAp, frozen, rz0, done_factor, pr);
     const int stride = gridDim.x * rows_per_block;
     int row = blockIdx.x * rows_per_block + local;
-    // two rows per step: eight independent 16-byte loads in flight per thread
-    for (; row + stride < n; row += 2 * stride) {
-      const size_t i0 = (size_t)row * Q + q, i1 = (size_t)(row + stride) * Q + q;
-      const float4 p0 = P[i0], p1 = P[i1], ap0 = AP[i0], ap1 = AP[i1];
-      float4 r0 = R[i0], r1 = R[i1], x0 = Xd[i0], x1 = Xd[i1];
-      const float d0 = invd[row], d1 = invd[row + stride];
-      // a dead column (alpha = 0) is left untouched: its p / Ap may hold inf or nan after float32 underflow
-      if (al[0] != 0.f) { x0.x += al[0] * p0.x; x1.x += al[0] * p1.x; r0.x -= al[0] * ap0.x; r1.x -= al[0] * ap1.x; }
-      if (al[1] != 0.f) { x0.y += al[1] * p0.y; x1.y += al[1] * p1.y; r0.y -= al[1] * ap0.y; r1.y -= al[1] * ap1.y; }
-      if (al[2] != 0.f) { x0.z += al[2] * p0.z; x1.z += al[2] * p1.z; r0.z -= al[2] * ap0.z; r1.z -= al[2] * ap1.z; }
-      if (al[3] != 0.f) { x0.w += al[3] * p0.w; x1.w += al[3] * p1.w; r0.w -= al[3] * ap0.w; r1.w -= al[3] * ap1.w; }
-      Xd[i0] = x0; Xd[i1] = x1; R[i0] = r0; R[i1] = r1;
-      // float64 products: r can sit far below sqrt(FLT_MIN) on quickly converging columns
-      const double e0 = (double)d0, e1 = (double)d1;
-      acc[0] += (double)r0.x * (double)r0.x * e0 + (double)r1.x * (double)r1.x * e1;
-      acc[1] += (double)r0.y * (double)r0.y * e0 + (double)r1.y * (double)r1.y * e1;
-      acc[2] += (double)r0.z * (double)r0.z * e0 + (double)r1.z * (double)r1.z * e1;
-      acc[3] += (double)r0.w * (double)r0.w * e0 + (double)r1.w * (double)r1.w * e1;
+    // four rows per step: eight independent 16-byte loads in flight per thread
+    for (; row + 3 * stride < n; row += 4 * stride) {
+      size_t i[4];
+      float4 ap[4], r[4];
+      float d[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) i[u] = (size_t)(row + u * stride) * Q + q;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { ap[u] = AP[i[u]]; r[u] = R[i[u]]; d[u] = invd[row + u * stride]; }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        // a dead column (alpha = 0) is left untouched: its Ap may hold inf or nan after float32 underflow
+        if (al[0] != 0.f) r[u].x -= al[0] * ap[u].x;
+        if (al[1] != 0.f) r[u].y -= al[1] * ap[u].y;
+        if (al[2] != 0.f) r[u].z -= al[2] * ap[u].z;
+        if (al[3] != 0.f) r[u].w -= al[3] * ap[u].w;
+        R[i[u]] = r[u];
+        // float64 products: r can sit far below sqrt(FLT_MIN) on quickly converging columns
+        const double e = (double)d[u];
+        acc[0] += (double)r[u].x * (double)r[u].x * e; acc[1] += (double)r[u].y * (double)r[u].y * e;
+        acc[2] += (double)r[u].z * (double)r[u].z * e; acc[3] += (double)r[u].w * (double)r[u].w * e;
+      }
     }
     for (; row < n; row += stride) {
       const size_t i = (size_t)row * Q + q;
-      const float4 p = P[i], ap = AP[i];
-      float4 r = R[i], x = Xd[i];
+      const float4 ap = AP[i];
+      float4 r = R[i];
       const float d = invd[row];
-      if (al[0] != 0.f) { x.x += al[0] * p.x; r.x -= al[0] * ap.x; }
-      if (al[1] != 0.f) { x.y += al[1] * p.y; r.y -= al[1] * ap.y; }
-      if (al[2] != 0.f) { x.z += al[2] * p.z; r.z -= al[2] * ap.z; }
-      if (al[3] != 0.f) { x.w += al[3] * p.w; r.w -= al[3] * ap.w; }
-      Xd[i] = x; R[i] = r;
+      if (al[0] != 0.f) r.x -= al[0] * ap.x;
+      if (al[1] != 0.f) r.y -= al[1] * ap.y;
+      if (al[2] != 0.f) r.z -= al[2] * ap.z;
+      if (al[3] != 0.f) r.w -= al[3] * ap.w;
+      R[i] = r;
       const double e = (double)d;
       acc[0] += (double)r.x * (double)r.x * e; acc[1] += (double)r.y * (double)r.y * e;
       acc[2] += (double)r.z * (double)r.z * e; acc[3] += (double)r.w * (double)r.w * e;
@@ -219,9 +222,14 @@ __global__ void k_scatter_columns(size_t n, int Kw, int Kfull, const int* __rest
   if (dk >= 0) Xfull[row * Kfull + dk] = Xw[i];
 }
 
-// beta = rz_next / rz ; p = D^-1 r + beta p ; block 0 clears the accumulators of the coming iterations
+// xd += alpha p ; beta = rz_next / rz ; p = D^-1 r + beta p ; block 0 clears the accumulators of the coming iterations.
+// x is carried as a float64 base X plus a float32 increment xd that k_flush_x folds into X before every float64
+// true-residual evaluation (an fp32 x alone stalls the true residual at 1e-4, SURVEY.md H5; the increment of
+// `check_every` iterations is small next to x, so its float32 rounding is far below the tolerance) - 8 instead of
+// 16 bytes of x traffic per element and iteration, and the update lives here because this kernel reads p anyway.
 __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __restrict__ R, float4* __restrict__ P,
-                                                 const float* __restrict__ invd, const double* __restrict__ rz,
+                                                 float4* __restrict__ Xd, const float* __restrict__ invd,
+                                                 const double* __restrict__ rz, const double* __restrict__ pAp,
                                                  const double* __restrict__ rz_next, double* __restrict__ clear_a,
                                                  double* __restrict__ clear_b, const int* __restrict__ frozen,
                                                  const double* __restrict__ rz0, double done_factor,
@@ -231,9 +239,10 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
   if (blockIdx.x == 0)
     for (int i = threadIdx.x; i < 4 * Q; i += blockDim.x) { clear_a[i] = 0.0; clear_b[i] = 0.0; }
   if (local >= rows_per_block) return;
-  float be[4];
+  float be[4], al[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
+    al[j] = pcg_alpha(4 * q + j, rz, pAp, frozen, rz0, done_factor, pr);  // the step k_pcg_update just took
     const double den = rz[4 * q + j], num = rz_next[4 * q + j];
     // after a replacement whose p is not even a descent direction for the new r (p.r <= 0): restart from z
     const bool live = den > done_factor * rz0[4 * q + j] && den > 0.0 && !frozen[4 * q + j] && !(pr && pr[4 * q + j] <= 0.0);
@@ -245,23 +254,31 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
   for (; row + stride < n; row += 2 * stride) {
     const size_t i0 = (size_t)row * Q + q, i1 = (size_t)(row + stride) * Q + q;
     const float4 r0 = R[i0], r1 = R[i1];
-    float4 p0 = P[i0], p1 = P[i1];
+    float4 p0 = P[i0], p1 = P[i1], x0 = Xd[i0], x1 = Xd[i1];
     const float d0 = invd[row], d1 = invd[row + stride];
-    // beta == 0 restarts the direction without reading the old p (which may hold inf / nan on a dead column)
+    // alpha == 0 / beta == 0 never touch the old p (which may hold inf / nan on a dead column)
+    if (al[0] != 0.f) { x0.x += al[0] * p0.x; x1.x += al[0] * p1.x; }
+    if (al[1] != 0.f) { x0.y += al[1] * p0.y; x1.y += al[1] * p1.y; }
+    if (al[2] != 0.f) { x0.z += al[2] * p0.z; x1.z += al[2] * p1.z; }
+    if (al[3] != 0.f) { x0.w += al[3] * p0.w; x1.w += al[3] * p1.w; }
     p0.x = r0.x * d0 + (be[0] != 0.f ? be[0] * p0.x : 0.f); p0.y = r0.y * d0 + (be[1] != 0.f ? be[1] * p0.y : 0.f);
     p0.z = r0.z * d0 + (be[2] != 0.f ? be[2] * p0.z : 0.f); p0.w = r0.w * d0 + (be[3] != 0.f ? be[3] * p0.w : 0.f);
     p1.x = r1.x * d1 + (be[0] != 0.f ? be[0] * p1.x : 0.f); p1.y = r1.y * d1 + (be[1] != 0.f ? be[1] * p1.y : 0.f);
     p1.z = r1.z * d1 + (be[2] != 0.f ? be[2] * p1.z : 0.f); p1.w = r1.w * d1 + (be[3] != 0.f ? be[3] * p1.w : 0.f);
-    P[i0] = p0; P[i1] = p1;
+    P[i0] = p0; P[i1] = p1; Xd[i0] = x0; Xd[i1] = x1;
   }
   for (; row < n; row += stride) {
     const size_t i = (size_t)row * Q + q;
     const float4 r = R[i];
-    float4 p = P[i];
+    float4 p = P[i], x = Xd[i];
     const float d = invd[row];
+    if (al[0] != 0.f) x.x += al[0] * p.x;
+    if (al[1] != 0.f) x.y += al[1] * p.y;
+    if (al[2] != 0.f) x.z += al[2] * p.z;
+    if (al[3] != 0.f) x.w += al[3] * p.w;
     p.x = r.x * d + (be[0] != 0.f ? be[0] * p.x : 0.f); p.y = r.y * d + (be[1] != 0.f ? be[1] * p.y : 0.f);
     p.z = r.z * d + (be[2] != 0.f ? be[2] * p.z : 0.f); p.w = r.w * d + (be[3] != 0.f ? be[3] * p.w : 0.f);
-    P[i] = p;
+    P[i] = p; Xd[i] = x;
   }
 }
 
@@ -494,7 +511,7 @@ int spmm_plan_ring(tcs_ctx* ctx, tcs_system& S) {
   SpmmRing T;
   memset(&T, 0, sizeof T);
   const int rowbytes = 16 * Q;
-  T.G = 32 / Q;
+  T.G = std::min(16, 32 / Q);  // 16-byte rows: 16 rows per warp step keep the tile (and its stage buffers) at 256 rows
   T.R = kRingWarps * T.G;
   T.S = std::min(8, std::max(2, env_int("TCS_RING_S", 3)));
   T.dup = (Q == 4 && env_int("TCS_RING_DUP", 1)) ? 1 : 0;
@@ -766,6 +783,17 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     int samples = 0;
     converged = 0;
     int it = 0;
+    // TCS_DEBUG: wall-clock per phase (we synchronise at every check, so host time brackets device time)
+    auto phase_t0 = std::chrono::steady_clock::now();
+    int phase_it0 = 0;
+    auto phase_report = [&](const char* what) {
+      if (!getenv("TCS_DEBUG")) return;
+      const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - phase_t0).count();
+      fprintf(stderr, "[tcs] %s: iterations %d..%d at width %d, kernel %d: %.1f ms = %.1f us / iteration\n", what, phase_it0, it,
+              Kw, S.ring ? 3 : S.tiled ? 2 : 1, ms, it > phase_it0 ? 1e3 * ms / (it - phase_it0) : 0.0);
+      phase_t0 = std::chrono::steady_clock::now();
+      phase_it0 = it;
+    };
     while (it < opts.max_iterations) {
       const int chunk = std::min(opts.check_every, opts.max_iterations - it);
       for (int j = 0; j < chunk; ++j, ++it) {
@@ -776,10 +804,10 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp0);
         if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
         ++spmm_launches;
-        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Qw, P4, AP4, R4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
-               d_pAp + s0 * Kp0, d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr);
-        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Qw, R4, P4, invd.p, d_rz + s0 * Kp0, d_rz + s1 * Kp0,
-               d_pAp + s1 * Kp0, d_rz + s2 * Kp0, frozen.p, d_rz0, done_factor, pr);
+        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
+               d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr);
+        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
+               d_pAp + s0 * Kp0, d_rz + s1 * Kp0, d_pAp + s1 * Kp0, d_rz + s2 * Kp0, frozen.p, d_rz0, done_factor, pr);
       }
       // fold the float32 increment into the float64 solution; the float64 true residual replaces the recurrence
       // residual, and rz of the coming iteration is recomputed from it
@@ -807,10 +835,11 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         for (int k = 0; k < K; ++k) fprintf(stderr, " %.2e", rel[k]);
         fprintf(stderr, "\n");
       }
-      if (active_cols == 0) { converged = 1; break; }
+      if (active_cols == 0) { converged = 1; phase_report("done"); break; }
       const int newKw = std::max(4, (active_cols + 3) & ~3);
       if (compact_enabled && newKw < Kw && it < opts.max_iterations) {
         // ---- drop the converged columns
+        phase_report("compaction");
         if (!S.X.p) {
           TRY(S.X.alloc(ctx, nk));
           CK(cudaMemsetAsync(S.X.p, 0, nk * 8, ctx->stream));
@@ -854,6 +883,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         TRY(spmm_plan(ctx, S));
         B4 = (const float4*)Bw.p; P4 = (float4*)S.P.p; R4 = (float4*)S.R.p; AP4 = (float4*)S.AP.p;
         if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] it=%d: %d columns left, working width %d\n", it, active_cols, Kw);
+        phase_report("re-plan");
       } else {
         CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
       }
