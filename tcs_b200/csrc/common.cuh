@@ -98,7 +98,10 @@ struct SpmmTile {
 // shape of k_spmm_ring (spmm_ring.cuh): contiguous tile range per CTA, sliding ring window of P, S-stage TMA pipeline
 struct SpmmRing {
   int R;          // rows per tile = consumer warps x G
-  int G;          // rows per warp step = 32 / Q
+  int G;          // rows per warp step = 32 / Qp
+  int Qp;         // lanes per row group (= Q, or 4 for 48-byte rows padded to a 64-byte pitch)
+  int fill_async; // ring rows arrive by 16-byte cp.async instead of TMA bulk copies (needed when pitch != 16 Q)
+  int pitch;      // bytes between ring rows in shared memory (16 Q, or 64 when padded)
   int H;          // halo rows on either side of a tile that are guaranteed to be in the ring
   int S;          // pipeline stages (tiles in flight)
   int ring_rows;  // power of two

@@ -511,10 +511,18 @@ int spmm_plan_ring(tcs_ctx* ctx, tcs_system& S) {
   SpmmRing T;
   memset(&T, 0, sizeof T);
   const int rowbytes = 16 * Q;
-  T.G = std::min(16, 32 / Q);  // 16-byte rows: 16 rows per warp step keep the tile (and its stage buffers) at 256 rows
+  // 48-byte rows (9..12 columns) have no conflict-free placement (18 M bank conflicts on C4, 190 us).  TCS_RING_PAD=1
+  // pads them to a 64-byte pitch in shared memory and runs them like 64-byte rows with one idle lane per row group;
+  // a bulk copy cannot pad, and filling the ring with 16-byte cp.async instead costs more (+28 us measured on 64-byte
+  // rows) than the conflicts it removes (196 us), so it stays off.
+  const bool pad = Q == 3 && env_int("TCS_RING_PAD", 0);
+  T.Qp = pad ? 4 : Q;
+  T.pitch = pad ? 64 : rowbytes;
+  T.fill_async = pad ? 1 : 0;
+  T.G = std::min(16, 32 / T.Qp);  // 16-byte rows: 16 rows per warp step keep the tile (and its stage buffers) at 256 rows
   T.R = kRingWarps * T.G;
   T.S = std::min(8, std::max(2, env_int("TCS_RING_S", 3)));
-  T.dup = (Q == 4 && env_int("TCS_RING_DUP", 1)) ? 1 : 0;
+  T.dup = (T.pitch == 64 && env_int("TCS_RING_DUP", 1)) ? 1 : 0;
   const int ntiles = (n + T.R - 1) / T.R;
   // small systems are launch-bound and stay with the other kernels (TCS_RING_MIN_TILES=1 forces the ring, for tests)
   if (ntiles < env_int("TCS_RING_MIN_TILES", 4 * ctx->sm_count)) return TCS_OK;
@@ -552,7 +560,7 @@ int spmm_plan_ring(tcs_ctx* ctx, tcs_system& S) {
     T.off_far = T.off_cv + T.cap * 6;
     T.stage_bytes = (T.off_far + farcap * rowbytes + 127) & ~127;
     T.off_ring = T.off_stage0 + T.S * T.stage_bytes;
-    T.ring_bytes = ring_rows * rowbytes;
+    T.ring_bytes = ring_rows * T.pitch;
     T.total = T.off_ring + T.ring_bytes * (T.dup ? 2 : 1) + (T.dup ? 128 : 0);
     return T.total;
   };

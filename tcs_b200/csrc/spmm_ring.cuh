@@ -111,7 +111,7 @@ __global__ void k_ring_fill(int n, int Q, SpmmRing T, int ntiles, const uint32_t
   float* wout = (float*)(b + (size_t)entries * 2) + (sl & 0xFFFFu) + g;
   const int L = (int)(sl >> 16);
   const int stage = t % T.S;  // a tile's stage is its global index mod S: independent of the CTA ranges
-  const int rowbytes = 16 * Q, mask = T.ring_rows - 1;
+  const int rowbytes = 16 * Q, pitch = T.pitch, mask = T.ring_rows - 1;
   const int far_base = T.off_stage0 + stage * T.stage_bytes + T.off_far;
   const int ring2 = T.off_ring + T.ring_bytes + 64;
   uint32_t a = 0, a1 = 0;
@@ -119,7 +119,7 @@ __global__ void k_ring_fill(int n, int Q, SpmmRing T, int ntiles, const uint32_t
   if (row < n) {
     a = rowptr[row];
     a1 = rowptr[row + 1];
-    own = ((T.dup && ((row ^ pos) & 1)) ? ring2 : T.off_ring) + (row & mask) * rowbytes;
+    own = ((T.dup && ((row ^ pos) & 1)) ? ring2 : T.off_ring) + (row & mask) * pitch;
   }
   for (int k = 0; k < L; ++k, ++a) {
     int off = own;
@@ -131,8 +131,8 @@ __global__ void k_ring_fill(int n, int Q, SpmmRing T, int ntiles, const uint32_t
       if (c < 0) off = far_base + (-1 - c) * rowbytes;
       // second ring copy when the neighbour row would land in the other half of the 128-byte line than the one
       // this row group (position parity) reads: the two groups of a quarter warp never meet
-      else if (T.dup && ((c ^ pos) & 1)) off = ring2 + (c & mask) * rowbytes;
-      else off = T.off_ring + (c & mask) * rowbytes;
+      else if (T.dup && ((c ^ pos) & 1)) off = ring2 + (c & mask) * pitch;
+      else off = T.off_ring + (c & mask) * pitch;
     }
     off16[(size_t)k * T.G] = (uint16_t)(off >> 4);
     wout[(size_t)k * T.G] = w;
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
   double* red = (double*)(smem + T.off_red);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t0 = cta_ptr[blockIdx.x], t1 = cta_ptr[blockIdx.x + 1];  // contiguous tile range, balanced by work
-  const int rowbytes = 16 * Q, mask = T.ring_rows - 1;
+  const int rowbytes = 16 * Q, pitch = T.pitch, mask = T.ring_rows - 1;
   const int metabytes = ring_meta_bytes(T.R);
   if (threadIdx.x == 0) {
     for (int s = 0; s < T.S; ++s) {
@@ -174,7 +174,8 @@ __global__ void __launch_bounds__(kRingThreads, 1)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  const int g = lane / Q, q = lane - g * Q;
+  // Qp lanes per row group (Qp = Q, or 4 for the padded 48-byte rows: lane 3 of every group idles)
+  const int g = lane / T.Qp, q = lane - g * T.Qp;
   double acc[4] = {0.0, 0.0, 0.0, 0.0};
   bool active = false;
   int s = t0 % T.S;   // stage of tile t = t mod S; jm = j mod S and kq = (j / S) & 1 count its uses inside this CTA
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
     const int pid = threadIdx.x - 32 * kRingWarps;
     const int pw = pid >> 5;
     unsigned char* ring = smem + T.off_ring + (pw == 2 ? T.ring_bytes + 64 : 0);
-    const int qshift = (Q & (Q - 1)) == 0 ? __ffs(Q) - 1 : -1;
+    const uint32_t qmagic = (uint32_t)((0x100000000ull + (unsigned)Q - 1u) / (unsigned)Q);  // u / Q = umulhi(u, qmagic), u < 2^29
     int hi_prev = 0;
     uint4 d0 = desc[t0], d1 = desc[t0 + 1];
     if (pid == 96) {  // id list of the first tile
@@ -216,7 +217,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         mbar_expect_tx(&full[s], (uint32_t)metabytes + d0.y * 6u);
         bulk_g2s(st + T.off_meta, meta + (size_t)t * metabytes, (uint32_t)metabytes, &full[s]);
         if (d0.y) bulk_g2s(st + T.off_cv, blob + (size_t)d0.x * 6, d0.y * 6u, &full[s]);
-      } else if (pid == 32 || (pid == 64 && T.dup)) {
+      } else if (!T.fill_async && (pid == 32 || (pid == 64 && T.dup))) {
         const int r0 = t * T.R, r1 = min(n, r0 + T.R);
         const int lo = j == 0 ? max(0, r0 - T.H) : hi_prev;
         const int hi = max(lo, min(n, r1 + T.H));
@@ -229,13 +230,30 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         }
         hi_prev = hi;
       }
+      if (T.fill_async) {
+        // padded ring rows (48-byte rows at a 64-byte pitch): a bulk copy cannot pad, so all producer threads fill
+        // the ring with 16-byte cp.async, both copies
+        const int r0 = t * T.R, r1 = min(n, r0 + T.R);
+        const int lo = j == 0 ? max(0, r0 - T.H) : hi_prev;
+        const int hi = max(lo, min(n, r1 + T.H));
+        unsigned char* rg0 = smem + T.off_ring;
+        const uint32_t nrc = (uint32_t)(hi - lo) * (uint32_t)Q;
+        for (uint32_t u = pid; u < nrc; u += kRingProducers) {
+          const uint32_t i = __umulhi(u, qmagic), ch = u - i * (uint32_t)Q;
+          const int x = lo + (int)i;
+          const float4* src = &P[(size_t)x * Q + ch];
+          unsigned char* dst = rg0 + (size_t)(x & mask) * pitch + ch * 16u;
+          cp_async16(dst, src);
+          if (T.dup) cp_async16(dst + T.ring_bytes + 64, src);
+        }
+        hi_prev = hi;
+      }
       // far rows of this tile
       mbar_wait(&idbar[j & 1], (uint32_t)(j >> 1) & 1u);
       const int* ids = (const int*)(smem + T.off_ids + (j & 1) * T.ids_bytes) + (d0.z & 3u);
       const uint32_t nch = (d0.w - d0.z) * (uint32_t)Q;
       for (uint32_t u = pid; u < nch; u += kRingProducers) {
-        const uint32_t i = qshift >= 0 ? u >> qshift : u / (uint32_t)Q;
-        const uint32_t ch = u - i * (uint32_t)Q;
+        const uint32_t i = __umulhi(u, qmagic), ch = u - i * (uint32_t)Q;
         cp_async16(st + T.off_far + u * 16u, &P[(size_t)ids[i] * Q + ch]);
       }
       asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[s])) : "memory");
@@ -245,7 +263,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
     }
   } else {
     // ---------------------------------------------------------------- consumer warps: one row per Q-lane group
-    active = g < T.G;
+    active = g < T.G && q < Q;
     const int pos = warp * T.G + g;
     const unsigned char* Pq = smem + q * 16;
     const int own_ring2 = T.off_ring + T.ring_bytes + 64;
@@ -262,7 +280,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         const uint16_t* off_s = (const uint16_t*)(st + T.off_cv) + (sl & 0xFFFFu) + g;
         const float* w_s = (const float*)(st + T.off_cv + entries * 2u) + (sl & 0xFFFFu) + g;
         const int own = (T.dup && ((row ^ pos) & 1)) ? own_ring2 : T.off_ring;
-        const float4 p = *(const float4*)(Pq + own + (row & mask) * rowbytes);
+        const float4 p = *(const float4*)(Pq + own + (row & mask) * pitch);
         const float d = ((const float*)(st + T.off_meta + kRingMetaHdr + 2 * T.R))[lr];
         float4 y = make_float4(d * p.x, d * p.y, d * p.z, d * p.w);
 #pragma unroll 4

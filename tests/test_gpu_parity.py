@@ -192,11 +192,12 @@ def test_spmm_kernels_agree(ctx, shape, monkeypatch):
     out = {}
     envs = (("generic", 1, {"TCS_SPMM": "v1"}), ("tiled", 2, {"TCS_SPMM": "tiled"}),
             ("ring", 3, {"TCS_RING_MIN_TILES": "1"}),
+            ("ring_pad", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_PAD": "1"}),
             ("ring_s2_nodup", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "2", "TCS_RING_DUP": "0", "TCS_RING_ROWS": "1024"}),
             ("ring_s4_small", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "4", "TCS_RING_ROWS": "2048", "TCS_RING_FAR": "8",
                                   "TCS_RING_DUP": "0"}))
     for name, kid, env in envs:
-        for k in ("TCS_SPMM", "TCS_RING_MIN_TILES", "TCS_RING_S", "TCS_RING_DUP", "TCS_RING_ROWS", "TCS_RING_FAR"):
+        for k in ("TCS_SPMM", "TCS_RING_MIN_TILES", "TCS_RING_S", "TCS_RING_DUP", "TCS_RING_ROWS", "TCS_RING_FAR", "TCS_RING_PAD"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
