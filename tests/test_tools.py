@@ -1,0 +1,141 @@
+"""The headless tools: tcs_random_walker_segmentation (the reference's app without the viewer)
+and tcs_segmentation_evaluation, plus the C++ PCD reader / writer they share (include/tcs/pcd_io.h)."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from tcs_b200 import pcd
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CPP = os.path.join(ROOT, "tcs_b200", "cpp")
+APP = os.path.join(CPP, "tcs_random_walker_segmentation")
+EVAL = os.path.join(CPP, "tcs_segmentation_evaluation")
+
+
+def _build():
+    subprocess.check_call(["make", "-C", CPP, "-s"])
+
+
+def _expected_errors(gt, seg, finite):
+    """Reference rule (src/segmentation_evaluation.cpp:139-165) with an independent assignment solver (scipy)."""
+    from scipy.optimize import linear_sum_assignment
+    gt, seg = gt[finite], seg[finite]
+    gl, gi = np.unique(gt, return_inverse=True)
+    sl, si = np.unique(seg, return_inverse=True)
+    w = np.zeros((len(gl), len(sl)), np.int64)
+    np.add.at(w, (gi, si), 1)
+    r, c = linear_sum_assignment(w, maximize=True)
+    assigned = np.zeros(len(gl), np.int64)          # unassigned ground-truth labels map to segmentation label 0
+    assigned[r] = sl[c]
+    return int(np.count_nonzero(seg != assigned[gi])), int(w[r, c].sum())
+
+
+def _run_eval(tmp_path, gt, seg, xyz, mode):
+    a, b = str(tmp_path / ("seg_%s.pcd" % mode)), str(tmp_path / ("gt_%s.pcd" % mode))
+    f32 = lambda k: np.ascontiguousarray(xyz[:, k], np.float32)
+    pcd.write_pcd(a, {"x": f32(0), "y": f32(1), "z": f32(2), "label": seg.astype(np.uint32)}, mode=mode)
+    pcd.write_pcd(b, {"x": f32(0), "y": f32(1), "z": f32(2), "label": gt.astype(np.uint32)}, mode=mode)
+    err = str(tmp_path / "errors.pcd")
+    r = subprocess.run([EVAL, a, b, "--errors", err], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    pts = int(re.search(r"Points: (\d+)", r.stdout).group(1))
+    bad = int(re.search(r"Erroneous points: (\d+)", r.stdout).group(1))
+    flags, _ = pcd.read_pcd(err)                      # written by the C++ writer (binary), read by the Python reader
+    return pts, bad, flags["label"]
+
+
+@pytest.mark.parametrize("mode", ["ascii", "binary", "binary_compressed"])
+def test_evaluation_tool_and_pcd_io(tmp_path, mode):
+    _build()
+    rng = np.random.default_rng(5)
+    n = 4000
+    xyz = rng.normal(size=(n, 3)).astype(np.float32)
+    xyz[rng.random(n) < 0.1] = np.nan                  # non-finite ground-truth points are skipped
+    gt = rng.integers(0, 6, n)
+    seg = (gt * 7 + 3) % 11                            # a relabelling ...
+    flip = rng.random(n) < 0.07
+    seg[flip] = rng.integers(0, 11, int(flip.sum()))   # ... with 7 % noise and more segmentation labels than truth
+    finite = np.isfinite(xyz).all(axis=1)
+    pts, bad, flags = _run_eval(tmp_path, gt, seg, xyz, mode)
+    want, _ = _expected_errors(gt, seg, finite)
+    assert pts == int(finite.sum()) and bad == want
+    assert int(flags.sum()) == bad and not flags[~finite].any()
+    import orc
+    assert orc.segmentation_error(gt[finite].astype(np.uint32), seg[finite].astype(np.uint32)) == bad
+
+
+def test_evaluation_more_truth_labels_than_segments(tmp_path):
+    """Unassigned ground-truth labels map to segmentation label 0 (std::map::operator[] in the reference)."""
+    _build()
+    gt = np.array([1, 1, 1, 2, 2, 3, 3, 3, 3], np.uint32)
+    seg = np.array([5, 5, 0, 5, 0, 0, 0, 9, 9], np.uint32)
+    xyz = np.zeros((9, 3), np.float32)
+    pts, bad, _ = _run_eval(tmp_path, gt, seg, xyz, "ascii")
+    want, _ = _expected_errors(gt, seg, np.ones(9, bool))
+    assert pts == 9 and bad == want
+
+
+def test_cpp_reader_on_reference_scene(tmp_path):
+    """LZF streams with real back references: the reference's own data/test1.pcd scored against itself."""
+    src = "/root/reference/data/test1.pcd"
+    if not os.path.exists(src):
+        pytest.skip("reference data not mounted")
+    _build()
+    r = subprocess.run([EVAL, src, src], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    d = np.load(os.path.join(ROOT, "tests", "golden", "scene_test1.npz"))
+    finite = np.isfinite(d["xyz"]).all(axis=1)
+    assert int(re.search(r"Points: (\d+)", r.stdout).group(1)) == int(finite.sum())
+    assert int(re.search(r"Erroneous points: (\d+)", r.stdout).group(1)) == 0
+
+
+def test_app_refuses_to_run_without_seeds_or_gpu(tmp_path):
+    _build()
+    cloud = str(tmp_path / "c.pcd")
+    pcd.write_pcd(cloud, {"x": np.zeros(4, np.float32), "y": np.zeros(4, np.float32), "z": np.ones(4, np.float32)})
+    r = subprocess.run([APP, cloud], capture_output=True, text=True)
+    assert r.returncode == 2 and "--load-seeds" in r.stderr          # no viewer: seeds must come from a file
+    import torch
+    if not torch.cuda.is_available():
+        seeds = str(tmp_path / "s.pcd")
+        pcd.write_pcd(seeds, {"x": np.zeros(1, np.float32), "y": np.zeros(1, np.float32), "z": np.ones(1, np.float32),
+                              "label": np.ones(1, np.uint32)})
+        r = subprocess.run([APP, cloud, "--load-seeds", seeds, "--save"], capture_output=True, text=True, cwd=str(tmp_path))
+        assert r.returncode == 3 and "no CPU fallback" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,res", [("test1", 0.006), ("test1", 0.01), ("test47", 0.006)])
+def test_app_matches_oracle_and_scores(scenes, tmp_path, name, res):
+    """BASELINE configs 1-3: <scene>.pcd [-v R] --load-seeds seeds.pcd --save, then the evaluation tool on the result."""
+    import orc
+    from tcs_b200.seeds import seeds_from_labels
+    _build()
+    sc = scenes[name]
+    xyz, rgba, label = sc["xyz"], sc["rgba"], sc["label"]
+    sx, sl, _ = seeds_from_labels(xyz, label, sc["id"], 5)
+    cloud, seeds, out = str(tmp_path / "scene.pcd"), str(tmp_path / "seeds.pcd"), str(tmp_path / "segmentation.pcd")
+    f = lambda a, k: np.ascontiguousarray(a[:, k], np.float32)
+    pcd.write_pcd(cloud, {"x": f(xyz, 0), "y": f(xyz, 1), "z": f(xyz, 2), "rgba": rgba.astype(np.uint32),
+                          "label": label.astype(np.uint32)}, width=640, height=480)
+    pcd.write_pcd(seeds, {"x": f(sx, 0), "y": f(sx, 1), "z": f(sx, 2), "label": sl.astype(np.uint32)}, mode="ascii")
+    r = subprocess.run([APP, cloud, "--load-seeds", seeds, "--save", "--out", out, "--format", "binary", "-v", repr(res)],
+                       capture_output=True, text=True, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout + r.stderr
+    got, hdr = pcd.read_pcd(out)
+    assert hdr["n"] == len(xyz)
+    ref = orc.segment_cloud(xyz, rgba, res, sx, sl, preset=1, solver=orc.SOLVE_LDLT_F64)   # the CLI pipeline
+    p2v = ref["graph"].point_to_vertex()
+    want = np.where(p2v == 0xFFFFFFFF, 0, ref["vertex_colour"][np.minimum(p2v, ref["graph"].V - 1)])
+    bad = int(np.count_nonzero(got["label"] != want))
+    assert bad <= 10 * max(3, ref["graph"].V // 2000), bad
+    # the evaluation tool on the saved file agrees with the rule evaluated in Python
+    r = subprocess.run([EVAL, out, cloud], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    finite = np.isfinite(xyz).all(axis=1)
+    expect, _ = _expected_errors(label.astype(np.int64), got["label"].astype(np.int64), finite)
+    assert int(re.search(r"Erroneous points: (\d+)", r.stdout).group(1)) == expect
+    assert expect < 0.05 * finite.sum()               # 5 seeds per label segment these scenes to > 95 %
