@@ -93,7 +93,7 @@ class ClockSampler(threading.Thread):
                 self.rows.append([c.strip() for c in out.strip().split(",")])
             except Exception:
                 pass
-            self._halt.wait(0.2)
+            self._halt.wait(1.0)   # nvidia-smi queries perturb the GPU: sample sparsely
 
     def stop(self):
         self._halt.set()

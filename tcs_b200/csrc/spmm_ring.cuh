@@ -193,7 +193,8 @@ __global__ void __launch_bounds__(kRingThreads, 1)
     const int pid = threadIdx.x - 32 * kRingWarps;
     const int pw = pid >> 5;
     unsigned char* ring = smem + T.off_ring + (pw == 2 ? T.ring_bytes + 64 : 0);
-    const uint32_t qmagic = (uint32_t)((0x100000000ull + (unsigned)Q - 1u) / (unsigned)Q);  // u / Q = umulhi(u, qmagic), u < 2^29
+    // u / Q = umulhi(u, qmagic) for u < 2^29 and Q >= 2 (Q = 1 would need 2^32: handled apart)
+    const uint32_t qmagic = Q > 1 ? (uint32_t)((0x100000000ull + (unsigned)Q - 1u) / (unsigned)Q) : 0u;
     int hi_prev = 0;
     uint4 d0 = desc[t0], d1 = desc[t0 + 1];
     if (pid == 96) {  // id list of the first tile
@@ -239,7 +240,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         unsigned char* rg0 = smem + T.off_ring;
         const uint32_t nrc = (uint32_t)(hi - lo) * (uint32_t)Q;
         for (uint32_t u = pid; u < nrc; u += kRingProducers) {
-          const uint32_t i = __umulhi(u, qmagic), ch = u - i * (uint32_t)Q;
+          const uint32_t i = (Q > 1 ? __umulhi(u, qmagic) : u), ch = u - i * (uint32_t)Q;
           const int x = lo + (int)i;
           const float4* src = &P[(size_t)x * Q + ch];
           unsigned char* dst = rg0 + (size_t)(x & mask) * pitch + ch * 16u;
@@ -253,7 +254,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
       const int* ids = (const int*)(smem + T.off_ids + (j & 1) * T.ids_bytes) + (d0.z & 3u);
       const uint32_t nch = (d0.w - d0.z) * (uint32_t)Q;
       for (uint32_t u = pid; u < nch; u += kRingProducers) {
-        const uint32_t i = __umulhi(u, qmagic), ch = u - i * (uint32_t)Q;
+        const uint32_t i = (Q > 1 ? __umulhi(u, qmagic) : u), ch = u - i * (uint32_t)Q;
         cp_async16(st + T.off_far + u * 16u, &P[(size_t)ids[i] * Q + ch]);
       }
       asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[s])) : "memory");
