@@ -1,0 +1,205 @@
+"""GPU known-answer and edge-case tests through the C ABI: hand-solvable graphs (closed-form potentials, the same
+cases that pin the oracle in test_oracle_kat.py), degenerate inputs the reference handles (empty / all-NaN clouds,
+seedless and isolated parts, every vertex seeded, clouds without colour), random graphs against the oracle's direct
+solve, and size-independent properties at BASELINE's full C4 size."""
+import numpy as np
+import pytest
+
+import orc
+from tcs_b200 import capi
+from tcs_b200.seeds import seeds_from_labels
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = capi.Context(0)
+    yield c
+    c.close()
+
+
+def _path(ctx, n, w=None):
+    xyz = np.zeros((n, 3), np.float32)
+    xyz[:, 0] = np.arange(n)
+    return ctx.graph_from_edges(xyz, np.arange(1, n, dtype=np.uint32), np.arange(0, n - 1, dtype=np.uint32),
+                                weight=np.ones(n - 1, np.float32) if w is None else w)
+
+
+def test_path_graph_linear_potentials(ctx):
+    n = 11
+    g = _path(ctx, n)
+    colours = np.zeros(n, np.uint32)
+    colours[0], colours[-1] = 1, 2
+    st, out, pot, info = g.random_walker(colours, 2, want_potentials=True)
+    assert st == 0 and info.as_dict()["converged"]
+    expect = 1.0 - np.arange(n) / (n - 1.0)
+    np.testing.assert_allclose(pot[:, 0], expect, atol=2e-6)
+    np.testing.assert_allclose(pot[:, 1], 1.0 - expect, atol=2e-6)
+    assert list(out[:5]) == [1] * 5 and list(out[6:]) == [2] * 5 and out[5] in (1, 2)   # exact tie at the midpoint
+
+
+def test_weighted_path_is_a_resistor_chain(ctx):
+    w = np.array([1.0, 0.5, 0.25, 2.0], np.float32)
+    g = _path(ctx, 5, w)
+    st, out, pot, _ = g.random_walker(np.array([1, 0, 0, 0, 2], np.uint32), 2, want_potentials=True)
+    r = 1.0 / w
+    np.testing.assert_allclose(pot[:, 0], 1.0 - np.concatenate([[0], np.cumsum(r)]) / r.sum(), atol=2e-6)
+
+
+def test_star_graph_weighted_average(ctx):
+    g = ctx.graph_from_edges(np.zeros((5, 3), np.float32), np.array([1, 2, 3, 4], np.uint32), np.zeros(4, np.uint32),
+                             weight=np.array([1.0, 2.0, 3.0, 4.0], np.float32))
+    st, out, pot, _ = g.random_walker(np.array([0, 1, 1, 2, 3], np.uint32), 3, want_potentials=True)
+    np.testing.assert_allclose(pot[0], [0.3, 0.3, 0.4], atol=2e-6)
+    assert st == 0 and out[0] == 3
+
+
+def test_seedless_component_and_isolated_vertex(ctx):
+    """impl/random_walker.hpp:191-192: a component without seeds stays unlabelled; zero-degree vertices are no rows."""
+    src = np.array([1, 2, 3, 5, 6], np.uint32)
+    tgt = np.array([0, 1, 2, 4, 5], np.uint32)
+    g = ctx.graph_from_edges(np.zeros((8, 3), np.float32), src, tgt, weight=np.ones(5, np.float32))   # vertex 7 isolated
+    nc, comp = g.components()
+    assert nc == 3 and list(comp) == [0, 0, 0, 0, 1, 1, 1, 2]
+    st, out, pot, info = g.random_walker(np.array([0, 2, 0, 0, 0, 0, 0, 0], np.uint32), 2, want_potentials=True)
+    assert st == 0 and list(out) == [2, 2, 2, 2, 0, 0, 0, 0]
+    assert np.all(pot[4:] == 0) and info.as_dict()["rows"] == 6
+
+
+def test_every_vertex_seeded_and_no_seeds(ctx):
+    g = _path(ctx, 6)
+    colours = np.array([1, 2, 1, 2, 1, 2], np.uint32)
+    st, out, _, info = g.random_walker(colours, 2)
+    assert st == 0 and list(out) == list(colours) and info.as_dict()["rows"] == 0 and info.as_dict()["iterations"] == 0
+    st, out, _, _ = g.random_walker(np.zeros(6, np.uint32), 0)
+    assert st == 0 and not out.any()
+
+
+def test_colour_out_of_range_is_an_error(ctx):
+    g = _path(ctx, 4)
+    with pytest.raises(capi.TcsError):
+        g.random_walker(np.array([1, 0, 0, 5], np.uint32), 2)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_random_graph_against_the_oracle_direct_solve(ctx, seed):
+    """Random sparse graphs with weights over five decades, 7 labels: potentials vs the oracle's float64 LDL^T."""
+    rng = np.random.default_rng(seed)
+    n, m = 3000, 12000
+    a, b = rng.integers(0, n, m), rng.integers(0, n, m)
+    keep = a != b
+    e = np.unique(np.stack([np.maximum(a, b)[keep], np.minimum(a, b)[keep]], axis=1), axis=0)
+    src, tgt = e[:, 0].astype(np.uint32), e[:, 1].astype(np.uint32)
+    w = (10.0 ** rng.uniform(-5, 0, len(src))).astype(np.float32)
+    xyz = rng.normal(size=(n, 3)).astype(np.float32)
+    colours = np.zeros(n, np.uint32)
+    colours[rng.choice(n, 70, replace=False)] = rng.integers(1, 8, 70)
+    g = ctx.graph_from_edges(xyz, src, tgt, weight=w)
+    o = orc.Graph.from_edges(xyz, src, tgt, weight=w)
+    st, cg, pg, info = g.random_walker(colours, 7, want_potentials=True)
+    so, co, po, _ = o.random_walker(colours, 7, solver=orc.SOLVE_LDLT_F64, want_potentials=True)
+    assert st == 0 and so == 0 and max(info.as_dict()["rel_residual"]) <= 1e-6
+    assert np.abs(pg - po).max() < 1e-3
+    assert np.count_nonzero(cg != co) <= 3
+
+
+def test_empty_and_all_nan_clouds(ctx):
+    """voxel_grid_graph_builder.hpp:72-77: bad input gives an empty graph, no throw; segmenting it labels nothing."""
+    for xyz in (np.zeros((0, 3), np.float32), np.full((100, 3), np.nan, np.float32)):
+        ctx.upload_cloud(xyz, np.zeros(len(xyz), np.uint32))
+        g = ctx.build_voxel_graph(0.006)
+        assert (g.V, g.E) == (0, 0)
+        g.close()
+        r = ctx.segment_cloud(0.006, np.zeros((1, 3), np.float32), np.array([1], np.uint32))
+        assert r["graph"].V == 0 and (len(xyz) == 0 or np.all(r["point_cluster"] == 1))   # everything in the nil cluster
+        r["graph"].close()
+
+
+def test_single_voxel_cloud(ctx):
+    xyz = np.full((10, 3), 1.0, np.float32)
+    xyz[:, 0] += np.linspace(0, 1e-4, 10, dtype=np.float32)
+    ctx.upload_cloud(xyz, np.full(10, 0xFF808080, np.uint32))
+    o = orc.Graph.from_cloud(xyz, np.full(10, 0xFF808080, np.uint32), 0.006)
+    g = ctx.build_voxel_graph(0.006)
+    assert (g.V, g.E) == (o.V, o.E) and np.array_equal(g.point_to_vertex(), o.point_to_vertex())
+    g.close()
+
+
+def test_cloud_without_colour_matches_oracle(ctx, scenes):
+    """PointXYZ input: the RGB term is dropped (EdgeWeightComputer::addTerm on a colourless point type)."""
+    sc = scenes["test13"]
+    sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
+    ctx.upload_cloud(sc["xyz"], None)
+    r = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
+    ref = orc.segment_cloud(sc["xyz"], None, 0.006, sx, sl, preset=0, mode=orc.MODE_PARITY, solver=orc.SOLVE_LDLT_F64)
+    assert r["status"] == capi.OK and r["info"].as_dict()["converged"]
+    bad = int(np.count_nonzero(r["vertex_colour"] != ref["vertex_colour"]))
+    assert bad <= max(3, r["graph"].V // 2000), bad
+    r["graph"].close()
+
+
+def test_c5_batch_matches_oracle(ctx):
+    """BASELINE configs[4] shape: a few of the 1024 synthetic 640x480 scenes, each against the oracle."""
+    from tcs_b200 import synth
+    for i in (1, 2, 3):
+        xyz, rgba, label = synth.make_c5(i)
+        sx, sl, _ = seeds_from_labels(xyz, label, i, 5)
+        ctx.upload_cloud(xyz, rgba)
+        r = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
+        ref = orc.segment_cloud(xyz, rgba, 0.006, sx, sl, preset=0, mode=orc.MODE_PARITY, solver=orc.SOLVE_LDLT_F64)
+        g, o = r["graph"], ref["graph"]
+        assert (g.V, g.E) == (o.V, o.E)
+        for a, b in zip(g.csr(), o.csr()):
+            assert np.array_equal(a, b)
+        assert r["info"].as_dict()["converged"]
+        bad = int(np.count_nonzero(r["vertex_colour"] != ref["vertex_colour"]))
+        assert bad <= max(3, g.V // 2000), (i, bad)
+        g.close()
+
+
+def test_c4_full_size_properties(ctx):
+    """BASELINE configs[3] at full size (10 M points, 2.85 M vertices, 16 labels), through properties that need no
+    oracle run: every column meets the float64 residual bound, potentials are a partition of unity on seeded
+    components, seeds keep their labels, the SpMM kernel equals the generic one on random data, a second run is
+    idempotent up to near-ties, and the label image agrees with the generating scene."""
+    from tcs_b200 import synth
+    xyz, rgba, label = synth.make_c4()
+    sx, sl, _ = seeds_from_labels(xyz, label, 0, 10)
+    ctx.upload_cloud(xyz, rgba)
+    r = ctx.segment_cloud(0.005, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST,
+                          opts=capi.default_opts(store_potentials=1))
+    info = r["info"].as_dict()
+    g = r["graph"]
+    assert r["status"] == capi.OK and info["converged"] and max(info["rel_residual"]) <= 1e-6
+    assert info["spmm_kernel"] == 3 and info["ncolours"] == 16 and g.V > 2_000_000
+    K = info["ncolours"]
+    pot = np.zeros((K, g.V), np.float32)
+    capi.lib().tcs_graph_download_potentials(g.h, pot.ctypes.data)
+    vc = r["vertex_colour"]
+    labelled = vc > 0
+    s = pot.sum(axis=0)
+    # a residual of 1e-6 leaves errors of up to ~1e-1 in weakly coupled pockets of these ill-conditioned systems
+    # (SURVEY.md H5), so the bound on the worst row is loose and the bulk is checked separately
+    dev = np.abs(s[labelled] - 1.0)
+    assert dev.max() < 0.25 and np.quantile(dev, 0.999) < 5e-2 and pot.min() > -0.05 and pot.max() < 1.05
+    assert np.all(pot[:, ~labelled] == 0)
+    near = g.nearest_vertices(sx)
+    want = 1 + np.searchsorted(np.unique(sl), sl)
+    last = {}
+    for v, c in zip(near, want):            # later seeds overwrite earlier ones on the same vertex
+        last[int(v)] = int(c)
+    assert all(vc[v] == c for v, c in last.items())
+    diff, ref, dot, kernel = g.check_spmm(7)
+    assert kernel == 3 and diff <= 2e-5 * ref and dot < 1e-6
+    # agreement with the generating labels (majority label per vertex) - 10 seeds per label segment this scene well
+    p2v = g.point_to_vertex()
+    ok = p2v != 0xFFFFFFFF
+    point_colour = np.zeros(len(p2v), np.int64)
+    point_colour[ok] = vc[p2v[ok]]
+    truth = 1 + np.searchsorted(np.unique(sl), label)
+    assert np.count_nonzero(point_colour[ok] == truth[ok]) > 0.9 * ok.sum()
+    g.close()
+    r2 = ctx.segment_cloud(0.005, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST)
+    assert np.count_nonzero(r2["vertex_colour"] != vc) <= max(10, info["near_ties"] + len(vc) // 100000)
+    r2["graph"].close()
