@@ -43,6 +43,10 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--small", action="store_true", help="debug: 1280x960 scene instead of the full C4 shape")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard", default="scenes", choices=["scenes", "columns"],
+                    help="N > 1: 'scenes' = one scene per GPU (weak scaling, no collective, the default); 'columns' = ONE "
+                         "scene, its label columns split over the GPUs, one NCCL all-gather of (best potential, colour) "
+                         "per vertex (strong scaling)")
     return ap.parse_args()
 
 
@@ -131,7 +135,7 @@ def run_reference(args, rank, world):
     print(json.dumps({
         "impl": "reference", "metric": "rw_segmentation_vertices_per_s", "value": val, "unit": "vertices/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong" if columns else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
         "cpu_baseline": {"value": val, "unit": "vertices/s", "cores": 1, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "vertices/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -155,7 +159,8 @@ def run_ours(args, rank, local_rank, world):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    w, h, xyz, rgba, label, sx, sl = make_scene(args, rank)
+    columns = args.shard == "columns" and world > 1
+    w, h, xyz, rgba, label, sx, sl = make_scene(args, 0 if columns else rank)
     n = len(xyz)
     stream = torch.cuda.Stream()
     ctx = capi.Context(local_rank, stream=stream.cuda_stream)
@@ -168,6 +173,17 @@ def run_ours(args, rank, local_rank, world):
     pc_host = torch.empty(n, dtype=torch.int32).pin_memory()
     vc_host = torch.empty(n, dtype=torch.int32).pin_memory()
     opts = capi.default_opts(time_spmm=1)
+    if columns:     # ONE scene: this rank solves its block of label columns
+        from tcs_b200 import shard
+        opts.column_begin, opts.column_count = shard.columns_for_rank(len(np.unique(sl)), rank, world)
+        if opts.column_count == 0:
+            raise SystemExit("bench.py: more ranks than label columns")
+
+    def merge(graph):
+        """The shard's one exchange: all-gather of (best potential, colour) per vertex over NCCL, merged on device."""
+        if columns:
+            val, col = graph.best()
+            shard._merge_best_nccl(val, col, world)
 
     def barrier():
         torch.cuda.synchronize()
@@ -178,6 +194,7 @@ def run_ours(args, rank, local_rank, world):
     def step_resident():
         ctx.set_device_cloud(dev_cloud.data_ptr(), n, True)
         r = ctx.segment_cloud(C4_RES, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST, opts=opts, want_host=False)
+        merge(r["graph"])
         return r
 
     def step_e2e():
@@ -193,7 +210,9 @@ def run_ours(args, rank, local_rank, world):
                                  len(sll), C.byref(opts), C.c_void_p(pc_host.data_ptr()),
                                  C.c_void_p(vc_host.data_ptr()), C.byref(info), C.byref(gh))
         ctx.check(st)
-        return dict(graph=capi.Graph(ctx, gh), info=info)
+        g = capi.Graph(ctx, gh)
+        merge(g)
+        return dict(graph=g, info=info)
 
     # ---- device-resident arm
     last = None
@@ -252,12 +271,17 @@ def run_ours(args, rank, local_rank, world):
         tv = torch.tensor([float(V), float(Ve), float(launches)], dtype=torch.float64, device="cuda")
         dist.all_reduce(tv, op=dist.ReduceOp.SUM)
         V_all, Ve_all, launches_all = tv.tolist()
+        if columns:     # one scene in total: its vertices count once
+            V_all, Ve_all = float(V), float(Ve)
     else:
         V_all, Ve_all, launches_all = float(V), float(Ve), float(launches)
     ms_max, ms_e2e_max = t[0].item(), t[1].item()
 
     if rank == 0:
         nrows, nnz, K = info["rows"], info["nnz"], info["ncolours"]
+        K_total = K
+        if columns:
+            K = opts.column_count       # the SpMM of this rank carries its own columns only
         b_spmm = 8 * nnz + 4 * (nrows + 1) + 8 * nrows * K          # SURVEY.md 8(d) / DESIGN.md
         avg_ms = spmm_ms / max(1, spmm_n)
         peaks = {}
@@ -271,16 +295,17 @@ def run_ours(args, rank, local_rank, world):
         traffic = None    # DRAM bytes per launch of that kernel from the committed ncu --set full capture
         try:
             tr = json.load(open(os.path.join(ROOT, "profiles", "spmm_traffic.json")))
-            if tr.get("kernel") == kname and not args.small:
+            if tr.get("kernel") == kname and not args.small and not columns:
                 traffic = int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])
         except Exception:
             pass
         out = {
             "metric": "rw_segmentation_vertices_per_s", "value": V_all / (ms_max * 1e-3), "unit": "vertices/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(workload_config(args, world), vertices=int(V // args.steps), edges=int(E), rows=nrows, nnz=nnz,
-                           labels=K, pcg_iterations_per_step=iters // args.steps, converged=converged,
+            "higher_is_better": True, "scaling": "strong" if columns else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": dict(workload_config(args, 1 if columns else world), shard="label columns of one scene, one NCCL "
+                           "all-gather per step" if columns else "independent scenes, no collective", vertices=int(V // args.steps), edges=int(E), rows=nrows, nnz=nnz,
+                           labels=K_total, pcg_iterations_per_step=iters // args.steps, converged=converged,
                            max_rel_residual=max(info["rel_residual"])),
             "e2e": {"value": Ve_all / (ms_e2e_max * 1e-3), "unit": "vertices/s", "h2d_bytes_per_step": 16 * n + 16 * len(sl),
                     "d2h_bytes_per_step": 4 * n + 4 * int(Ve // args.steps), "ms_per_step": ms_e2e_max / args.steps},

@@ -67,6 +67,12 @@ typedef struct tcs_solver_opts {
   int check_every;       /* iterations between float64 true-residual replacements / convergence checks; default 50 */
   int store_potentials;  /* keep the dense V x K potentials on the device (getPotentials) */
   int time_spmm;         /* bracket sampled SpMM launches with CUDA events (fills tcs_solve_info.spmm_ms) */
+  /* label-column shard: solve only the colour columns [column_begin, column_begin +
+   * column_count); column_count = 0 solves all.  All seeds stay boundary conditions; the other columns' potentials
+   * are reported as 0, vertices are labelled by the best column of THIS shard, and tcs_graph_download_best gives the
+   * (potential, colour) pairs a caller merges across shards (maximum potential, lowest colour on ties). */
+  int column_begin;
+  int column_count;
 } tcs_solver_opts;
 
 #define TCS_MAX_LABELS 64
@@ -164,6 +170,9 @@ int tcs_segment_cloud(tcs_ctx* ctx, float resolution, int preset, int mode, cons
 /* potentials kept by store_potentials (getPotentials, random_walker_segmentation.h:251): V x K column-major */
 int tcs_graph_download_potentials(tcs_graph* g, float* potentials);
 int tcs_graph_download_colours(tcs_graph* g, uint32_t* colours);
+/* per vertex: the largest potential among the solved columns and its colour (seeds: 1 and their colour; unlabelled
+ * vertices: 0 and 0) - what a label-column shard contributes to the merged labelling */
+int tcs_graph_download_best(tcs_graph* g, float* best_potential, uint32_t* best_colour);
 /* device-resident results (valid until the graph is destroyed) */
 const uint32_t* tcs_graph_d_colours(const tcs_graph* g);
 const int32_t* tcs_graph_d_point_cluster(const tcs_graph* g);

@@ -37,7 +37,7 @@ EXPORTS = [
     "tcs_graph_upload_weights", "tcs_normals", "tcs_smoothen", "tcs_signed_curvatures", "tcs_edge_weights",
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
-    "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm",
+    "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm", "tcs_graph_download_best",
 ]
 
 
@@ -47,7 +47,7 @@ class Term(C.Structure):
 
 class SolverOpts(C.Structure):
     _fields_ = [("tolerance", C.c_double), ("max_iterations", C.c_int), ("check_every", C.c_int),
-                ("store_potentials", C.c_int), ("time_spmm", C.c_int)]
+                ("store_potentials", C.c_int), ("time_spmm", C.c_int), ("column_begin", C.c_int), ("column_count", C.c_int)]
 
 
 class SolveInfo(C.Structure):
@@ -129,6 +129,7 @@ def lib():
     L.tcs_graph_d_point_cluster.argtypes = [vp]
     L.tcs_graph_d_point_cluster.restype = vp
     L.tcs_bench_spmm.argtypes = [vp, ci, C.POINTER(cf), C.POINTER(C.c_longlong)]
+    L.tcs_graph_download_best.argtypes = [vp, vp, vp]
     L.tcs_check_spmm.argtypes = [vp, C.c_uint, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                  C.POINTER(ci)]
     _lib = L
@@ -354,6 +355,12 @@ class Graph:
         c = np.zeros(self.V, np.uint32)
         self.ctx.check(lib().tcs_graph_download_colours(self.h, _p(c)))
         return c
+
+    def best(self):
+        """(best potential, its colour) per vertex among the columns this solve covered."""
+        val, col = np.zeros(self.V, np.float32), np.zeros(self.V, np.uint32)
+        self.ctx.check(lib().tcs_graph_download_best(self.h, _p(val), _p(col)))
+        return val, col
 
     def check_spmm(self, seed=1):
         d, r, dd, k = C.c_double(), C.c_double(), C.c_double(), C.c_int()

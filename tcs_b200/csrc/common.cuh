@@ -168,6 +168,7 @@ struct tcs_graph {
   // results
   DBuf<uint32_t> colours;        // V
   DBuf<int32_t> point_cluster;   // N
+  DBuf<float> best_val;          // V: largest potential among the solved columns (seeds: 1)
   DBuf<float> potentials;        // V x K column-major (store_potentials)
   int pot_K = 0;
   tcs_system sys;

@@ -334,28 +334,36 @@ __global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint3
 
 // assignColors (impl/random_walker.hpp:209-222): first maximal potential of the row; rows whose potentials are all
 // zero (seedless components, :191-192) stay unlabelled.  Also scatters potentials (getPotentials, :224-243).
-__global__ void k_argmax(int n, int K, int Kp, const double* __restrict__ X, const uint32_t* __restrict__ row_vertex,
-                         uint32_t* __restrict__ colours, float* __restrict__ potentials, size_t V,
-                         unsigned long long* __restrict__ near_ties) {
+__global__ void k_argmax(int n, int K, int Kp, int k0, int k1, const double* __restrict__ X,
+                         const uint32_t* __restrict__ row_vertex, uint32_t* __restrict__ colours,
+                         float* __restrict__ potentials, size_t V, unsigned long long* __restrict__ near_ties,
+                         float* __restrict__ best_val) {
   int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= n) return;
   const double* x = X + (size_t)r * Kp;
   const uint32_t v = row_vertex[r];
-  float best = (float)x[0], second = -INFINITY;
-  int bi = 0;
+  if (potentials)
+    for (int k = 0; k < K; ++k) potentials[(size_t)k * V + v] = (float)x[k];
+  // the maximum runs over the solved columns [k0, k1) only (all of them unless this is a label-column shard)
+  float best = (float)x[k0], second = -INFINITY;
+  int bi = k0;
   bool any = best != 0.0f;
-  if (potentials) potentials[v] = best;
-  for (int k = 1; k < K; ++k) {
+  for (int k = k0 + 1; k < k1; ++k) {
     float f = (float)x[k];
-    if (potentials) potentials[(size_t)k * V + v] = f;
     any = any || f != 0.0f;
     if (f > best) { second = best; best = f; bi = k; }
     else if (f > second) second = f;
   }
   if (any) {
     colours[v] = (uint32_t)bi + 1u;
-    if (K > 1 && best - second < 1e-6f) atomicAdd(near_ties, 1ull);
+    best_val[v] = best;
+    if (k1 - k0 > 1 && best - second < 1e-6f) atomicAdd(near_ties, 1ull);
   }
+}
+// best potential of the vertices that are not rows: seeds carry potential 1 for their colour, the rest 0
+__global__ void k_best_init(size_t V, const uint32_t* __restrict__ colours, float* __restrict__ best_val) {
+  size_t v = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  if (v < V) best_val[v] = colours[v] ? 1.0f : 0.0f;
 }
 
 __global__ void k_seed_potentials(size_t V, const uint32_t* __restrict__ seed_colour, float* __restrict__ potentials) {
@@ -374,6 +382,8 @@ extern "C" void tcs_solver_opts_default(tcs_solver_opts* o) {
   o->check_every = 50;
   o->store_potentials = 0;
   o->time_spmm = 0;
+  o->column_begin = 0;
+  o->column_count = 0;
 }
 
 namespace {
@@ -726,6 +736,8 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     g->pot_K = 0;
   }
 
+  TRY(g->best_val.alloc(ctx, V));
+  LAUNCH(ctx, k_best_init, div_up(V, 256), 256, 0, V, g->colours.p, g->best_val.p);
   int iterations = 0, converged = 1, kernel_at_start = 0;
   double rel[TCS_MAX_LABELS] = {0};
   float spmm_sum_ms = 0.f;
@@ -743,6 +755,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     std::vector<char> done(K, 0);
     const bool compact_enabled = env_int("TCS_COMPACT", 1) != 0;
     bool compacted = false;
+    bool dropped_columns = false;  // converged columns have left the working set (SpMM timing samples stop there)
     const size_t nk = (size_t)n * Kp0;
     DBuf<double> Xw;   // float64 solution of the working columns (becomes S.X when no compaction happens)
     DBuf<float> Xd;    // float32 increment since the last flush
@@ -802,12 +815,82 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
       phase_t0 = std::chrono::steady_clock::now();
       phase_it0 = it;
     };
+    // ---- re-pack the working set to the columns that are not done (newKw = their count rounded up to 4)
+    auto compact = [&](int newKw, int active_cols) -> int {
+      const size_t nkw = (size_t)n * Kw;
+      // ---- drop the converged columns
+      phase_report("compaction");
+      if (!S.X.p) {
+        TRY(S.X.alloc(ctx, nk));
+        CK(cudaMemsetAsync(S.X.p, 0, nk * 8, ctx->stream));
+      }
+      std::vector<int> cols(2 * (size_t)Kp0, -1), newmap;  // [0, Kp0): scatter targets; [Kp0, 2 Kp0): repack sources
+      for (int kw = 0; kw < Kw; ++kw) {
+        cols[kw] = wmap[kw];
+        if (wmap[kw] >= 0 && !done[wmap[kw]]) { cols[Kp0 + newmap.size()] = kw; newmap.push_back(wmap[kw]); }
+      }
+      newmap.resize(newKw, -1);
+      CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+      LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
+      const size_t nk2 = (size_t)n * newKw;
+      DBuf<float> P2, R2, B2, Xd2, AP2;
+      DBuf<double> X2;
+      TRY(P2.alloc(ctx, nk2)); TRY(R2.alloc(ctx, nk2)); TRY(B2.alloc(ctx, nk2)); TRY(Xd2.alloc(ctx, nk2));
+      TRY(AP2.alloc(ctx, nk2)); TRY(X2.alloc(ctx, nk2));
+      const int* src = d_cols.p + Kp0;
+      LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.P.p, P2.p);
+      LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.R.p, R2.p);
+      LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src,
+             Bw.p ? Bw.p : S.B.p, B2.p);
+      LAUNCH(ctx, k_repack_columns<double>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, Xw.p, X2.p);
+      CK(cudaMemsetAsync(Xd2.p, 0, nk2 * 4, ctx->stream));
+      // per-column scalars: same permutation on the host (we are at a synchronisation point anyway)
+      CK(cudaMemcpyAsync(h.data(), scal.p, (size_t)kScalRows * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));  // also: `cols` was read by the copy above
+      std::vector<double> h2((size_t)kScalRows * Kp0, 0.0);
+      for (int r8 = 0; r8 < kScalRows; ++r8)
+        for (int k2 = 0; k2 < newKw; ++k2)
+          if (cols[Kp0 + k2] >= 0) h2[(size_t)r8 * Kp0 + k2] = h[(size_t)r8 * Kp0 + cols[Kp0 + k2]];
+      CK(cudaMemcpyAsync(scal.p, h2.data(), (size_t)kScalRows * Kp0 * 8, cudaMemcpyHostToDevice, ctx->stream));
+      for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
+      CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));  // h2 is a local vector
+      S.P.swap(P2); S.R.swap(R2); S.AP.swap(AP2); Bw.swap(B2); Xw.swap(X2); Xd.swap(Xd2);
+      Kw = newKw; Qw = Kw / 4; wmap = newmap;
+      S.Kp = Kw;
+      compacted = true;
+      L = pcg_launch_shape(ctx, n, Qw);
+      TRY(spmm_plan(ctx, S));
+      B4 = (const float4*)Bw.p; P4 = (float4*)S.P.p; R4 = (float4*)S.R.p; AP4 = (float4*)S.AP.p;
+      if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] it=%d: %d columns left, working width %d\n", it, active_cols, Kw);
+      phase_report("re-plan");
+      return TCS_OK;
+    };
+    if (opts.column_count > 0 && (opts.column_begin > 0 || opts.column_begin + opts.column_count < K)) {
+      // label-column shard: the other columns count as done from the start
+      int mine = 0;
+      for (int k = 0; k < K; ++k) {
+        if (k < opts.column_begin || k >= opts.column_begin + opts.column_count) done[k] = 1;
+        else ++mine;
+      }
+      if (mine == 0) return tcs_fail(ctx, TCS_ERR_INPUT, "column shard [%d, %d) selects none of the %d colours", opts.column_begin,
+                                     opts.column_begin + opts.column_count, K);
+      const int newKw = std::max(4, (mine + 3) & ~3);
+      if (newKw < Kw) {
+        TRY(compact(newKw, mine));
+      } else {
+        for (int kw = 0; kw < Kw; ++kw)
+          if (wmap[kw] >= 0 && done[wmap[kw]]) h_frozen[kw] = 1;
+        CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+      }
+    }
     while (it < opts.max_iterations) {
       const int chunk = std::min(opts.check_every, opts.max_iterations - it);
       for (int j = 0; j < chunk; ++j, ++it) {
         const int s0 = it % 3, s1 = (it + 1) % 3, s2 = (it + 2) % 3;
         const double* pr = (j == 0 && it > 0) ? d_pr : nullptr;  // first step after a residual replacement
-        const bool timed = opts.time_spmm && samples < kMaxSamples && !compacted;
+        const bool timed = opts.time_spmm && samples < kMaxSamples && !dropped_columns;
         if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
         launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp0);
         if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
@@ -846,56 +929,15 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
       if (active_cols == 0) { converged = 1; phase_report("done"); break; }
       const int newKw = std::max(4, (active_cols + 3) & ~3);
       if (compact_enabled && newKw < Kw && it < opts.max_iterations) {
-        // ---- drop the converged columns
-        phase_report("compaction");
-        if (!S.X.p) {
-          TRY(S.X.alloc(ctx, nk));
-          CK(cudaMemsetAsync(S.X.p, 0, nk * 8, ctx->stream));
-        }
-        std::vector<int> cols(2 * (size_t)Kp0, -1), newmap;  // [0, Kp0): scatter targets; [Kp0, 2 Kp0): repack sources
-        for (int kw = 0; kw < Kw; ++kw) {
-          cols[kw] = wmap[kw];
-          if (wmap[kw] >= 0 && !done[wmap[kw]]) { cols[Kp0 + newmap.size()] = kw; newmap.push_back(wmap[kw]); }
-        }
-        newmap.resize(newKw, -1);
-        CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
-        LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
-        const size_t nk2 = (size_t)n * newKw;
-        DBuf<float> P2, R2, B2, Xd2, AP2;
-        DBuf<double> X2;
-        TRY(P2.alloc(ctx, nk2)); TRY(R2.alloc(ctx, nk2)); TRY(B2.alloc(ctx, nk2)); TRY(Xd2.alloc(ctx, nk2));
-        TRY(AP2.alloc(ctx, nk2)); TRY(X2.alloc(ctx, nk2));
-        const int* src = d_cols.p + Kp0;
-        LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.P.p, P2.p);
-        LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.R.p, R2.p);
-        LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src,
-               Bw.p ? Bw.p : S.B.p, B2.p);
-        LAUNCH(ctx, k_repack_columns<double>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, Xw.p, X2.p);
-        CK(cudaMemsetAsync(Xd2.p, 0, nk2 * 4, ctx->stream));
-        // per-column scalars: same permutation on the host (we are at a synchronisation point anyway)
-        CK(cudaMemcpyAsync(h.data(), scal.p, (size_t)kScalRows * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));  // also: `cols` was read by the copy above
-        std::vector<double> h2((size_t)kScalRows * Kp0, 0.0);
-        for (int r8 = 0; r8 < kScalRows; ++r8)
-          for (int k2 = 0; k2 < newKw; ++k2)
-            if (cols[Kp0 + k2] >= 0) h2[(size_t)r8 * Kp0 + k2] = h[(size_t)r8 * Kp0 + cols[Kp0 + k2]];
-        CK(cudaMemcpyAsync(scal.p, h2.data(), (size_t)kScalRows * Kp0 * 8, cudaMemcpyHostToDevice, ctx->stream));
-        for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
-        CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));  // h2 is a local vector
-        S.P.swap(P2); S.R.swap(R2); S.AP.swap(AP2); Bw.swap(B2); Xw.swap(X2); Xd.swap(Xd2);
-        Kw = newKw; Qw = Kw / 4; wmap = newmap;
-        S.Kp = Kw;
-        compacted = true;
-        L = pcg_launch_shape(ctx, n, Qw);
-        TRY(spmm_plan(ctx, S));
-        B4 = (const float4*)Bw.p; P4 = (float4*)S.P.p; R4 = (float4*)S.R.p; AP4 = (float4*)S.AP.p;
-        if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] it=%d: %d columns left, working width %d\n", it, active_cols, Kw);
-        phase_report("re-plan");
+        TRY(compact(newKw, active_cols));
+        dropped_columns = true;
       } else {
         CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
       }
     }
+    if (opts.column_count > 0)
+      for (int k = 0; k < K; ++k)
+        if (k < opts.column_begin || k >= opts.column_begin + opts.column_count) rel[k] = 0.0;  // not this shard's
     // the float64 solution of all columns, n x Kp0
     if (!compacted) {
       S.X.swap(Xw);
@@ -917,7 +959,10 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     DBuf<unsigned long long> ties;
     TRY(ties.alloc(ctx, 1));
     CK(cudaMemsetAsync(ties.p, 0, 8, ctx->stream));
-    LAUNCH(ctx, k_argmax, div_up(n, 256), 256, 0, n, K, Kp, S.X.p, S.row_vertex.p, g->colours.p, d_pot, V, ties.p);
+    int k0 = 0, k1 = K;
+    if (opts.column_count > 0) { k0 = std::max(0, opts.column_begin); k1 = std::min(K, opts.column_begin + opts.column_count); }
+    LAUNCH(ctx, k_argmax, div_up(n, 256), 256, 0, n, K, Kp, k0, k1, S.X.p, S.row_vertex.p, g->colours.p, d_pot, V, ties.p,
+           g->best_val.p);
     CK(cudaEventRecord(e_arg1, ctx->stream));
     CK(cudaMemcpyAsync(ctx->h_pin, ties.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
@@ -1072,5 +1117,17 @@ extern "C" int tcs_check_spmm(tcs_graph* g, unsigned seed, double* max_abs_diff,
   if (max_rel_dot_diff) *max_rel_dot_diff = rel;
   if (kernel) *kernel = S.ring ? 3 : S.tiled ? 2 : 1;
   CK(cudaGetLastError());
+  return TCS_OK;
+}
+
+extern "C" int tcs_graph_download_best(tcs_graph* g, float* best_potential, uint32_t* best_colour) {
+  if (!g) return TCS_ERR_INPUT;
+  tcs_ctx* ctx = g->ctx;
+  if (g->V == 0) return TCS_OK;
+  if (!g->best_val.p || !g->colours.p) return tcs_fail(ctx, TCS_ERR_STATE, "no solve on this graph yet");
+  CK(cudaSetDevice(ctx->device));
+  if (best_potential) CK(cudaMemcpyAsync(best_potential, g->best_val.p, 4 * g->V, cudaMemcpyDeviceToHost, ctx->stream));
+  if (best_colour) CK(cudaMemcpyAsync(best_colour, g->colours.p, 4 * g->V, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
   return TCS_OK;
 }

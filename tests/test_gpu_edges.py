@@ -203,3 +203,75 @@ def test_c4_full_size_properties(ctx):
     r2 = ctx.segment_cloud(0.005, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST)
     assert np.count_nonzero(r2["vertex_colour"] != vc) <= max(10, info["near_ties"] + len(vc) // 100000)
     r2["graph"].close()
+
+
+@pytest.mark.parametrize("world", [2, 3, 5])
+def test_label_column_shards_merge_to_the_full_solve(ctx, scenes, world):
+    """the label columns of one scene solved in `world` independent shards (here one after the
+    other on one GPU) and merged by (best potential, colour) give the labels of the all-columns solve."""
+    from tcs_b200 import shard
+    sc = scenes["test47"]                                   # 9 labels
+    sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
+    ctx.upload_cloud(sc["xyz"], sc["rgba"])
+    full = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY,
+                             opts=capi.default_opts(store_potentials=1))
+    K = full["info"].as_dict()["ncolours"]
+    fv, fc = full["graph"].best()
+    assert np.array_equal(fc, full["vertex_colour"])
+    vals, cols = [], []
+    for rank in range(world):
+        begin, count = shard.columns_for_rank(K, rank, world)
+        r = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY,
+                              opts=capi.default_opts(column_begin=begin, column_count=count, store_potentials=1))
+        info = r["info"].as_dict()
+        assert r["status"] == capi.OK and info["converged"] and max(info["rel_residual"]) <= 1e-6
+        g = r["graph"]
+        pot = np.zeros((K, g.V), np.float32)
+        capi.lib().tcs_graph_download_potentials(g.h, pot.ctypes.data)
+        rows = full["vertex_colour"] > 0
+        outside = np.ones(K, bool)
+        outside[begin:begin + count] = False
+        seeds_mask = np.zeros(g.V, bool)
+        seeds_mask[g.nearest_vertices(sx)] = True
+        assert np.all(pot[outside][:, ~seeds_mask] == 0)     # columns of other shards are not solved here
+        v, c = g.best()
+        assert np.all((c == 0) | ((c > begin) & (c <= begin + count)) | seeds_mask)
+        vals.append(v); cols.append(c)
+        g.close()
+    merged = shard.merge_best(np.stack(vals), np.stack(cols))
+    bad = int(np.count_nonzero(merged != full["vertex_colour"]))
+    assert bad <= max(3, len(merged) // 2000), bad
+    full["graph"].close()
+
+
+def test_label_column_shard_two_processes(tmp_path, scenes):
+    """Two ranks (two processes sharing this GPU, gloo for the one all-gather; NCCL when they own different GPUs)."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / "w.py"
+    script.write_text('''
+import os, sys
+sys.path.insert(0, %r); sys.path.insert(0, os.path.join(%r, "tests"))
+import numpy as np, torch.distributed as dist
+from tcs_b200 import capi, shard
+from tcs_b200.seeds import seeds_from_labels
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+d = np.load(os.path.join(%r, "tests", "golden", "scene_test56.npz"))     # 18 labels
+sx, sl, _ = seeds_from_labels(d["xyz"], d["label"], 3, 5)
+ctx = capi.Context(0)
+ctx.upload_cloud(d["xyz"], d["rgba"])
+merged, r = shard.segment_cloud_column_sharded(ctx, 0.006, sx, sl, rank, world, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
+assert r["info"].as_dict()["converged"]
+if rank == 0:
+    full = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
+    bad = int(np.count_nonzero(merged != full["vertex_colour"]))
+    assert bad <= max(3, len(merged) // 2000), bad
+    print("merged labels differ on", bad, "of", len(merged))
+dist.barrier()
+dist.destroy_process_group()
+''' % (root, root, root))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29543", str(script)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]

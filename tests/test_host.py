@@ -138,3 +138,38 @@ def test_combine_world_size_2_gloo(tmp_path):
     outs = [p.communicate(timeout=180)[0] for p in procs]
     assert all(p.returncode == 0 for p in procs), outs
     assert "ok 0 [0, 2, 4, 6]" in outs[0] and "ok 1 [1, 3, 5]" in outs[1]
+
+
+def test_column_shard_blocks_and_merge():
+    from tcs_b200 import shard
+    assert [shard.columns_for_rank(16, r, 8) for r in range(8)] == [(2 * r, 2) for r in range(8)]
+    blocks = [shard.columns_for_rank(18, r, 4) for r in range(4)]
+    assert blocks == [(0, 5), (5, 5), (10, 4), (14, 4)]
+    assert shard.columns_for_rank(3, 3, 4) == (3, 0)
+    # merge: largest potential wins, lowest colour on ties, unlabelled stays 0
+    val = np.array([[0.6, 0.5, 0.0, 0.2], [0.3, 0.5, 0.0, 0.7]], np.float32)
+    col = np.array([[1, 2, 0, 2], [3, 4, 0, 3]], np.uint32)
+    assert list(shard.merge_best(val, col)) == [1, 2, 0, 3]
+    assert list(shard.merge_best(val[::-1], col[::-1])) == [1, 2, 0, 3]
+
+
+def test_all_gather_best_world_size_2_gloo(tmp_path):
+    """The one exchange of the label-column shard, over gloo on CPU (NCCL on the GPU box)."""
+    script = tmp_path / "w.py"
+    script.write_text('''
+import os, sys
+sys.path.insert(0, %r)
+import numpy as np, torch.distributed as dist
+from tcs_b200 import shard
+dist.init_process_group("gloo")
+rank = dist.get_rank()
+val = np.array([0.9, 0.1, 0.5], np.float32) if rank == 0 else np.array([0.2, 0.8, 0.5], np.float32)
+col = np.array([1, 1, 2], np.uint32) if rank == 0 else np.array([3, 4, 3], np.uint32)
+gv, gc = shard.all_gather_best(val, col, 2)
+assert gv.shape == (2, 3) and list(shard.merge_best(gv, gc)) == [1, 4, 2]
+dist.destroy_process_group()
+''' % ROOT)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29541", str(script)],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
