@@ -118,6 +118,12 @@ int tcs_cloud_set_device(tcs_ctx* ctx, const void* d_xyzc, size_t n, int has_col
 /* VoxelGridGraphBuilder::compute, graph/impl/voxel_grid_graph_builder.hpp:69-143.
  * leaf_order_desc: 1 = PCL <= 1.8 leaf-iterator order (the reference's), 0 = ascending Morton order. */
 int tcs_build_voxel_graph(tcs_ctx* ctx, float resolution, int leaf_order_desc, tcs_graph** out);
+/* NearestNeighborsGraphBuilder::compute, graph/impl/nearest_neighbors_graph_builder.hpp:49-119:
+ * vertices = the finite points in index order; every vertex is joined to its num_neighbors (<= 64) nearest other
+ * points (use_radius = 0, useNearestKSearch) or to the nearest num_neighbors among the points with
+ * d^2 < (float)(radius^2) (use_radius = 1, useRadiusSearch); neighbours ordered by (d^2, index); edges in the
+ * reference's insertion order, each undirected edge once. */
+int tcs_build_nn_graph(tcs_ctx* ctx, int num_neighbors, double radius, int use_radius, tcs_graph** out);
 /* RandomWalkerSegmentation::setInputGraph (random_walker_segmentation.h:175): user graph, edges in insertion
  * order; rgba / normals4 / curvature / weight may be NULL. */
 int tcs_graph_create(tcs_ctx* ctx, size_t V, const float* xyz, const uint32_t* rgba, const float* normals4,

@@ -58,6 +58,11 @@ orc_graph* orc_build_voxel_graph(const float* xyz, const uint32_t* rgba, size_t 
 orc_graph* orc_graph_from_edges(size_t V, const float* xyz, const uint32_t* rgba, const float* normals4,
                                 const float* curvature, size_t E, const uint32_t* src, const uint32_t* tgt,
                                 const float* weight);
+/* graph/impl/nearest_neighbors_graph_builder.hpp:49-119: vertices = finite points in index order; edges to the
+ * num_neighbors nearest other points (use_radius = 0) or to the nearest num_neighbors among those with
+ * d^2 < (float)(radius^2) (use_radius = 1); neighbours ordered by (d^2, index), brute force. */
+orc_graph* orc_build_nn_graph(const float* xyz, const uint32_t* rgba, size_t n, int num_neighbors, double radius,
+                              int use_radius, int* status);
 void orc_graph_free(orc_graph* g);
 
 size_t orc_num_vertices(const orc_graph* g);

@@ -213,3 +213,63 @@ extern "C" orc_graph* orc_graph_from_edges(size_t V, const float* xyz, const uin
   g->build_out_edges();
   return g;
 }
+
+// ---- NearestNeighborsGraphBuilder::compute, graph/impl/nearest_neighbors_graph_builder.hpp:49-119 ------------------
+// Vertices are the finite points in index order (:58-72; copyPointCloud of the finite indices).  The copied cloud has
+// height 1, so the default search is always pcl::search::KdTree (:75-83), an exact FLANN search: per vertex the
+// num_neighbors + 1 nearest points (the first being the query itself, :95-97), or for RADIUS the nearest
+// num_neighbors + 1 among the points with d^2 < (float)(radius * radius) (:100-103; FLANN's RadiusResultSet keeps
+// dist < radius, and max_nn bounds the sorted result).  Distances are FLANN's L2_Simple<float>: ((dx*dx) + dy*dy) + dz*dz
+// in float32.  Restated here as a brute-force search; neighbours are ordered by (d^2, index) and the query vertex itself
+// is skipped (FLANN's order among equal distances is unspecified - with duplicated points the reference may return a
+// duplicate instead of the query as "first neighbour"; this restatement fixes the deterministic choice).  Edges are
+// added in the reference's loop order with its `if (!boost::edge(i, nb).second)` test (:105-107).
+extern "C" orc_graph* orc_build_nn_graph(const float* xyz, const uint32_t* rgba, size_t n, int num_neighbors,
+                                         double radius, int use_radius, int* status) {
+  if (status) *status = ORC_OK;
+  orc_graph* g = new orc_graph;
+  g->N = n;
+  g->has_color = rgba != nullptr;
+  g->p2v.assign(n, 0xFFFFFFFFu);
+  std::vector<uint32_t> finite;
+  for (size_t i = 0; i < n; ++i)
+    if (std::isfinite(xyz[3 * i]) && std::isfinite(xyz[3 * i + 1]) && std::isfinite(xyz[3 * i + 2])) finite.push_back((uint32_t)i);
+  const size_t V = finite.size();
+  g->alloc_vertices(V);
+  for (size_t v = 0; v < V; ++v) {
+    const size_t i = finite[v];
+    g->x[v] = xyz[3 * i]; g->y[v] = xyz[3 * i + 1]; g->z[v] = xyz[3 * i + 2];
+    if (rgba) g->rgba[v] = rgba[i];
+    g->p2v[i] = (uint32_t)v;   // :112-116
+  }
+  const size_t k = num_neighbors < 0 ? 0 : (size_t)num_neighbors;
+  const float r2 = (float)(radius * radius);
+  std::vector<std::vector<uint32_t>> nbr(V);
+  std::vector<std::pair<float, uint32_t>> cand;
+  for (size_t i = 0; i < V; ++i) {
+    cand.clear();
+    for (size_t j = 0; j < V; ++j) {
+      if (j == i) continue;
+      const float dx = g->x[i] - g->x[j], dy = g->y[i] - g->y[j], dz = g->z[i] - g->z[j];
+      const float d = dx * dx + dy * dy + dz * dz;
+      if (use_radius && !(d < r2)) continue;
+      cand.emplace_back(d, (uint32_t)j);
+    }
+    const size_t m = std::min(k, cand.size());
+    std::partial_sort(cand.begin(), cand.begin() + m, cand.end());
+    for (size_t j = 0; j < m; ++j) nbr[i].push_back(cand[j].second);
+  }
+  // boost::edge(i, nb, graph).second on an undirected graph: the edge exists if either endpoint added it before
+  std::vector<std::vector<uint32_t>> adj(V);
+  for (size_t i = 0; i < V; ++i)
+    for (uint32_t nb : nbr[i]) {
+      if (std::find(adj[i].begin(), adj[i].end(), nb) != adj[i].end()) continue;
+      adj[i].push_back(nb);
+      adj[nb].push_back((uint32_t)i);
+      g->esrc.push_back((uint32_t)i);
+      g->etgt.push_back(nb);
+    }
+  g->ew.assign(g->esrc.size(), 0.f);
+  g->build_out_edges();
+  return g;
+}

@@ -38,6 +38,7 @@ EXPORTS = [
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
     "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm", "tcs_graph_download_best",
+    "tcs_build_nn_graph",
 ]
 
 
@@ -99,6 +100,7 @@ def lib():
     L.tcs_cloud_upload.argtypes = [vp, vp, sz, vp, sz, sz]
     L.tcs_cloud_set_device.argtypes = [vp, vp, sz, ci]
     L.tcs_build_voxel_graph.argtypes = [vp, cf, ci, PP]
+    L.tcs_build_nn_graph.argtypes = [vp, ci, C.c_double, ci, PP]
     L.tcs_graph_create.argtypes = [vp, sz, vp, vp, vp, vp, sz, vp, vp, vp, PP]
     L.tcs_graph_destroy.argtypes = [vp]
     L.tcs_graph_destroy.restype = None
@@ -216,6 +218,12 @@ class Context:
     def build_voxel_graph(self, resolution: float, leaf_order_desc: int = 1) -> "Graph":
         h = C.c_void_p()
         self.check(lib().tcs_build_voxel_graph(self.h, resolution, leaf_order_desc, C.byref(h)))
+        return Graph(self, h)
+
+    def build_nn_graph(self, num_neighbors: int = 10, radius: float = 0.0, use_radius: bool = False) -> "Graph":
+        """NearestNeighborsGraphBuilder (kNN / radius) on the uploaded cloud."""
+        h = C.c_void_p()
+        self.check(lib().tcs_build_nn_graph(self.h, num_neighbors, radius, int(use_radius), C.byref(h)))
         return Graph(self, h)
 
     def graph_from_edges(self, xyz, src, tgt, weight=None, rgba=None, normals4=None, curvature=None) -> "Graph":

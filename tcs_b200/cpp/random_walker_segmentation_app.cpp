@@ -2,7 +2,7 @@
 // app_random_walker_segmentation (src/random_walker_segmentation_app.cpp:37-296) on the GPU path.
 //
 //   tcs_random_walker_segmentation <pcd-file> --load-seeds <pcd-file> [--save] [--save-clusters] [--potential]
-//       [-v res] [-z xyz] [-n normal] [-b curvature] [-c colour] [--weight-threshold t] [--convex-multiplier m]
+//       [--builder vg|nnk|nnr] [-v res] [--nn k] [--radius r] [-z xyz] [-n normal] [-b curvature] [-c colour] [--weight-threshold t] [--convex-multiplier m]
 //       [--out segmentation.pcd] [--format ascii|binary|binary_compressed]
 //
 // Same pipeline and option names / defaults as the reference (factory/edge_weight_computer_factory.h:20-46,
@@ -11,14 +11,17 @@
 // seeds; --save writes segmentation.pcd (labels = vertex colours, 0 for points without a vertex), --save-clusters
 // writes cluster%i.pcd.  There is no viewer on this box: interactive seed selection (and therefore --save-seeds) is
 // unavailable, the tool always behaves like --tv-no-gui, which the reference only allows together with --load-seeds
-// (:86-90).  Only the voxel-grid builder exists here (--builder nnk|nnr is rejected).
+// (:86-90).  --builder selects the voxel grid (default), the k-nearest (--nn, default 14) or the radius (--radius,
+// default 0.006) graph builder, as factory/graph_builder_factory.h:22-60 does.
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <chrono>
+#include <memory>
 #include <string>
 
 #include "tcs/evaluation.h"
+#include "tcs/graph/nearest_neighbors_graph_builder.h"
 #include "tcs/pcd_io.h"
 #include "tcs/random_walker_segmentation.h"
 
@@ -56,7 +59,8 @@ int main(int argc, char** argv) {
                  "--out <pcd-file> (default segmentation.pcd)\n--format ascii|binary|binary_compressed\n"
                  "Edge Weight Computer: -z <xyz influence 3.0> -n <normal influence 0.01> -b <curvature influence 0.0001>\n"
                  "  -c <color influence 3.0> --weight-threshold <1e-5> --convex-multiplier <0.01>\n"
-                 "Graph Builder: -v <voxel resolution 0.006> (--builder vg only)\n",
+                 "Graph Builder: --builder vg|nnk|nnr -v <voxel resolution 0.006> --nn <number of neighbors 14>\n"
+                 "  --radius <sphere radius 0.006>\n",
                  argv[0]);
     return 1;
   }
@@ -65,11 +69,13 @@ int main(int argc, char** argv) {
     std::fprintf(stderr, "No GUI mode can only be used with --load-seeds option.\n");
     return 2;
   }
-  const char* builder = value_of(argc, argv, "--builder");
-  if (builder && std::strcmp(builder, "vg")) {
-    std::fprintf(stderr, "builder '%s' is not available in this build (voxel grid only)\n", builder);
+  const std::string builder = value_of(argc, argv, "--builder") ? value_of(argc, argv, "--builder") : "vg";
+  if (builder != "vg" && builder != "nnk" && builder != "nnr") {
+    std::fprintf(stderr, "unknown builder type '%s' (vg, nnk, nnr)\n", builder.c_str());
     return 2;
   }
+  const int number_of_neighbors = (int)float_opt(argc, argv, "--nn", 14.0f);
+  const float radius = float_opt(argc, argv, "--radius", 0.006f);
   const bool option_save = has_switch(argc, argv, "--save"), option_save_clusters = has_switch(argc, argv, "--save-clusters");
   const bool mode_potential = has_switch(argc, argv, "--potential");
   const std::string out_name = value_of(argc, argv, "--out") ? value_of(argc, argv, "--out") : "segmentation.pcd";
@@ -97,14 +103,25 @@ int main(int argc, char** argv) {
     return 1;
   }
   std::printf("Edge Weight Computer: xyz influence %g, normal influence %g, curvature influence %g, color influence %g, "
-              "weight threshold %g, convex multiplier %g\nGraph Builder: VOXEL GRID, voxel resolution %g\n",
-              xyz, normal, curvature, color, threshold, convex, resolution);
+              "weight threshold %g, convex multiplier %g\n", xyz, normal, curvature, color, threshold, convex);
+  if (builder == "vg") std::printf("Graph Builder: VOXEL GRID, voxel resolution %g\n", resolution);
+  else if (builder == "nnk") std::printf("Graph Builder: NEAREST NEIGHBORS KNN, number of neighbors %d\n", number_of_neighbors);
+  else std::printf("Graph Builder: NEAREST NEIGHBORS RADIUS, sphere radius %g\n", radius);
 
   try {
     using namespace pcl::graph;
     typedef RWS::Graph Graph;
     RWS::GraphPtr g(new Graph);
-    VoxelGridGraphBuilder<PointT, Graph> gb(resolution);
+    std::unique_ptr<GraphBuilder<PointT, Graph>> gbp;
+    if (builder == "vg") {
+      gbp.reset(new VoxelGridGraphBuilder<PointT, Graph>(resolution));
+    } else {
+      NearestNeighborsGraphBuilder<PointT, Graph>* nn = new NearestNeighborsGraphBuilder<PointT, Graph>;
+      if (builder == "nnk") { nn->setNumberOfNeighbors(number_of_neighbors); nn->useNearestKSearch(); }
+      else { nn->setRadius(radius); nn->useRadiusSearch(); }
+      gbp.reset(nn);
+    }
+    GraphBuilder<PointT, Graph>& gb = *gbp;
     gb.setInputCloud(cloud);
     Stopwatch sw;
     gb.compute(*g);                         sw.lap("Building graph... ");

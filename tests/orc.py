@@ -47,6 +47,8 @@ def lib():
         L = _lib
         L.orc_build_voxel_graph.restype = vp
         L.orc_build_voxel_graph.argtypes = [vp, vp, sz, C.c_float, C.c_int, C.POINTER(C.c_int)]
+        L.orc_build_nn_graph.restype = vp
+        L.orc_build_nn_graph.argtypes = [vp, vp, sz, C.c_int, C.c_double, C.c_int, C.POINTER(C.c_int)]
         L.orc_graph_from_edges.restype = vp
         L.orc_graph_from_edges.argtypes = [sz, vp, vp, vp, vp, sz, vp, vp, vp]
         L.orc_graph_free.argtypes = [vp]
@@ -107,6 +109,15 @@ class Graph:
         xyz, rgba = _f32(xyz), _u32(rgba)
         st = C.c_int(0)
         h = lib().orc_build_voxel_graph(_p(xyz), _p(rgba), len(xyz), resolution, leaf_order_desc, C.byref(st))
+        g = Graph(h)
+        g.status = st.value
+        return g
+
+    @staticmethod
+    def from_cloud_nn(xyz, rgba, num_neighbors=10, radius=0.0, use_radius=False):
+        xyz, rgba = _f32(xyz), _u32(rgba)
+        st = C.c_int(0)
+        h = lib().orc_build_nn_graph(_p(xyz), _p(rgba), len(xyz), num_neighbors, radius, int(use_radius), C.byref(st))
         g = Graph(h)
         g.status = st.value
         return g

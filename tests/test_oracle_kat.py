@@ -211,3 +211,35 @@ def test_scene_sizes_match_the_survey(scenes):
         assert (g.V, g.E, g.depth) == (V, E, 8), name
     g = orc.Graph.from_cloud(scenes["test1"]["xyz"], scenes["test1"]["rgba"], 0.01)
     assert (g.V, g.E) == (16235, 104525)
+
+
+def test_nn_graph_known_answers():
+    """nearest_neighbors_graph_builder.hpp:49-119 on inputs whose answer is known by hand."""
+    nan = np.nan
+    # points on a line at 0, 1, 3, 7 (+ one non-finite point that gets no vertex)
+    xyz = np.array([[0, 0, 0], [nan, 0, 0], [1, 0, 0], [3, 0, 0], [7, 0, 0]], np.float32)
+    g = orc.Graph.from_cloud_nn(xyz, None, 1)
+    assert g.V == 4 and list(g.point_to_vertex()) == [0, 0xFFFFFFFF, 1, 2, 3]
+    s, t, _ = g.edges()
+    # v0 -> v1; v1 -> v0 (exists); v2 -> v1; v3 -> v2
+    assert list(zip(s, t)) == [(0, 1), (2, 1), (3, 2)]
+    g = orc.Graph.from_cloud_nn(xyz, None, 2)
+    s, t, _ = g.edges()
+    # v0: v1, v2; v1: v0 (exists), v2; v2: v1 (exists), v0 (exists); v3: v2, v1
+    assert list(zip(s, t)) == [(0, 1), (0, 2), (1, 2), (3, 2), (3, 1)]
+    # radius: strictly closer than the radius, at most num_neighbors of them
+    g = orc.Graph.from_cloud_nn(xyz, None, 10, 2.0, use_radius=True)
+    s, t, _ = g.edges()
+    assert list(zip(s, t)) == [(0, 1)]          # |v1 - v2| = 2 is not < 2
+    g = orc.Graph.from_cloud_nn(xyz, None, 1, 2.5, use_radius=True)
+    s, t, _ = g.edges()
+    assert list(zip(s, t)) == [(0, 1), (2, 1)]
+    # equidistant candidates: lower index first
+    sq = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [-1, 0, 0], [0, -1, 0]], np.float32)
+    g = orc.Graph.from_cloud_nn(sq, None, 2)
+    rp, col, _ = g.csr()
+    assert list(col[rp[0]:rp[1]][:2]) == [1, 2]
+    # more neighbours requested than points: complete graph
+    g = orc.Graph.from_cloud_nn(sq, None, 10)
+    assert g.E == 10
+    assert orc.Graph.from_cloud_nn(np.zeros((0, 3), np.float32), None, 10).V == 0

@@ -139,3 +139,42 @@ def test_app_matches_oracle_and_scores(scenes, tmp_path, name, res):
     expect, _ = _expected_errors(label.astype(np.int64), got["label"].astype(np.int64), finite)
     assert int(re.search(r"Erroneous points: (\d+)", r.stdout).group(1)) == expect
     assert expect < 0.05 * finite.sum()               # 5 seeds per label segment these scenes to > 95 %
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("builder", [["--builder", "nnk", "--nn", "8"], ["--builder", "nnr", "--radius", "0.02"]])
+def test_app_nearest_neighbour_builders(scenes, tmp_path, builder):
+    """--builder nnk|nnr (factory/graph_builder_factory.h:46-60): the app's labels equal those of the same pipeline
+    driven through the C ABI from Python on the same (subsampled) scene."""
+    from tcs_b200 import capi
+    from tcs_b200.seeds import seeds_from_labels
+    _build()
+    sc = scenes["test1"]
+    idx = (np.arange(0, 480, 2)[:, None] * 640 + np.arange(0, 640, 2)[None, :]).ravel()
+    xyz, rgba, label = sc["xyz"][idx].copy(), sc["rgba"][idx].copy(), sc["label"][idx].copy()
+    sx, sl, _ = seeds_from_labels(xyz, label, sc["id"], 5)
+    cloud, seeds, out = str(tmp_path / "scene.pcd"), str(tmp_path / "seeds.pcd"), str(tmp_path / "segmentation.pcd")
+    f = lambda a, k: np.ascontiguousarray(a[:, k], np.float32)
+    pcd.write_pcd(cloud, {"x": f(xyz, 0), "y": f(xyz, 1), "z": f(xyz, 2), "rgba": rgba.astype(np.uint32)}, width=320, height=240)
+    pcd.write_pcd(seeds, {"x": f(sx, 0), "y": f(sx, 1), "z": f(sx, 2), "label": sl.astype(np.uint32)}, mode="ascii")
+    r = subprocess.run([APP, cloud, "--load-seeds", seeds, "--save", "--out", out, "--format", "binary"] + builder,
+                       capture_output=True, text=True, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "NEAREST NEIGHBORS" in r.stdout
+    got, _ = pcd.read_pcd(out)
+    ctx = capi.Context(0)
+    ctx.upload_cloud(xyz, rgba)
+    g = ctx.build_nn_graph(8) if builder[1] == "nnk" else ctx.build_nn_graph(10, float(np.float32(0.02)), use_radius=True)
+    g.normals(); g.smoothen(); g.normals(); g.signed_curvatures()
+    g.edge_weights(capi.TERMS_CLI)
+    near = g.nearest_vertices(sx)
+    labels = np.unique(sl)
+    colours = np.zeros(g.V, np.uint32)
+    for s, v in enumerate(near):
+        colours[v] = 1 + int(np.searchsorted(labels, sl[s]))
+    st, cg, _, info = g.random_walker(colours, len(labels))
+    assert st == 0
+    p2v = g.point_to_vertex()
+    want = np.where(p2v == 0xFFFFFFFF, 0, cg[np.minimum(p2v, g.V - 1)])
+    assert np.count_nonzero(got["label"] != want) <= 3
+    ctx.close()
