@@ -90,7 +90,7 @@ def read_pcd(path: str) -> Tuple[Dict[str, np.ndarray], Dict[str, object]]:
     dts = [np.dtype(_TYPES[(t, s)]) for t, s in zip(types, sizes)]
     out: Dict[str, np.ndarray] = {}
     if mode == "ascii":
-        rows = np.loadtxt(blob[pos:].decode("ascii").splitlines(), dtype=np.float64, ndmin=2)
+        rows = np.loadtxt(blob[pos:].decode("ascii").splitlines()[:n], dtype=np.float64, ndmin=2)  # a graph file has an edge tail
         col = 0
         for name, dt, c in zip(fields, dts, counts):
             a = rows[:, col:col + c]

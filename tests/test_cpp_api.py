@@ -80,3 +80,29 @@ def test_cpp_api_matches_oracle(scenes, tmp_path, mode, name):
     lab = col > 0
     # (residual 1e-6 on these ill-conditioned systems leaves errors of ~1e-2 in the potentials)
     np.testing.assert_allclose(pot[lab].sum(axis=1), 1.0, atol=5e-2)
+
+
+GIO = os.path.join(ROOT, "tcs_b200", "cpp", "graph_io_check")
+
+
+def test_graph_io_and_subgraph_helpers_on_the_host(tmp_path):
+    """saveGraph / loadGraph (include/impl/io.hpp:13-101) and createSubgraphsFromColorMap / Indices
+    (graph/impl/common.hpp:151-239) need no device for a host-built graph."""
+    _build()
+    r = subprocess.run([GIO, str(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0 and "graph_io_check ok" in r.stdout, r.stdout + r.stderr
+    text = open(tmp_path / "graph.pcd").read()
+    head, tail = text.split("# Edges\n")
+    assert head.startswith("# .PCD v0.7") and "FIELDS x y z rgba normal_x normal_y normal_z curvature" in head
+    assert tail.splitlines()[:3] == ["0 1 1", "1 2 0.5", "2 3 1e-05"]
+    # the PCD part is a regular PCD file for any other reader
+    from tcs_b200 import pcd
+    cols, hdr = pcd.read_pcd(str(tmp_path / "graph.pcd"))
+    assert hdr["n"] == 7 and cols["rgba"][1] == 0xFF102030
+
+
+@pytest.mark.gpu
+def test_graph_io_round_trip_of_a_device_graph(tmp_path):
+    _build()
+    r = subprocess.run([GIO, str(tmp_path), "device"], capture_output=True, text=True)
+    assert r.returncode == 0 and "graph_io_check ok" in r.stdout, r.stdout + r.stderr
