@@ -91,7 +91,8 @@ typedef struct tcs_solve_info {
   float solve_ms;               /* device time of the whole PCG loop */
   float stage_ms[12];           /* build, normals, smoothen, normals2, signs, weights, components, seeds,
                                    assemble, solve, argmax, point labels (device time, CUDA events) */
-  int spmm_kernel;              /* which SpMM ran: 1 = k_spmm (generic), 2 = k_spmm_tiled, 3 = k_spmm_ring */
+  int spmm_kernel;              /* which SpMM ran: 1 = k_spmm (generic), 2 = k_spmm_tiled, 3 = k_spmm_ring,
+                                   4 = k_pcg_chunk (small systems: whole iterations in one persistent launch) */
 } tcs_solve_info;
 
 /* ---- context ------------------------------------------------------------------------------------------- */

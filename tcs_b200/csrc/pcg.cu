@@ -332,6 +332,251 @@ __global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint3
   reduce_columns(a_pr, q, Q, active, sm, pr);
 }
 
+// ---- small systems: `chunk` whole PCG iterations in ONE persistent launch -------------------------------------------
+// A 640 x 480 scene gives ~40 k rows.  With one launch per kernel an iteration costs ~20 us although it moves only a few
+// megabytes: every kernel is a chain of dependent L2 round trips (rowptr -> col -> P, scalars -> rows) on a handful of
+// rows per thread, plus three launches.  k_pcg_chunk keeps the system ON CHIP for a whole chunk of iterations: a thread
+// owns the same (at most M) rows throughout and holds their r, x increment, p and Ap in registers; the CSR slice of
+// the CTA's rows sits in shared memory; the only global traffic of an iteration is the gather of the neighbours' p
+// (read through L2, ld.global.cg), the store of the thread's own new p, and the per-column dot products.  The three
+// phases of an iteration (SpMM, residual update, direction update) are separated by grid-wide barriers (all CTAs are
+// co-resident: cooperative launch).  Same arithmetic, the same order of operations per row and the same fp64
+// accumulators as k_spmm / k_pcg_update / k_pcg_dir.
+__constant__ unsigned c_coop_sleep = 0;
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    target += gridDim.x;
+    // release: this CTA's writes (ordered before by the bar.sync) become visible before the count; acquire on the poll
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
+    unsigned seen;
+    while (true) {
+      asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(bar) : "memory");
+      if (seen >= target) break;
+      if (c_coop_sleep) __nanosleep(c_coop_sleep);   // hundreds of CTAs poll one L2 line: leave room for the arrivals
+    }
+  }
+  __syncthreads();
+}
+
+// Per-column dot products without atomics: every CTA reduces its threads' partial sums (fixed order: rows of a warp
+// lane-strided, then an xor tree) and stores them at part[blockIdx][column]; after the grid barrier every CTA adds the
+// gridDim.x partials of each column in the same fixed order.  Distinct addresses (no hot L2 line), and the sums - hence
+// the whole solve - are bitwise reproducible from run to run.
+__device__ __forceinline__ void chunk_block_partials(const double acc[4], int Q, double* arr, double* part) {
+  const int Kp = 4 * Q, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, rows_per_block = blockDim.x / Q;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) arr[threadIdx.x * 4 + j] = acc[j];
+  __syncthreads();
+  for (int c = warp; c < Kp; c += (int)(blockDim.x >> 5)) {
+    const int q = c >> 2, jj = c & 3;
+    double v = 0.0;
+    for (int l = lane; l < rows_per_block; l += 32) v += arr[(l * Q + q) * 4 + jj];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+    if (lane == 0) part[(size_t)blockIdx.x * Kp + c] = v;
+  }
+}
+__device__ __forceinline__ double chunk_column_total(const double* part, int Kp, int c) {
+  const int lane = threadIdx.x & 31;
+  // four independent loads in flight per lane (an L2 round trip each); fixed order of additions
+  double v0 = 0.0, v1 = 0.0, v2 = 0.0, v3 = 0.0;
+  const int G = (int)gridDim.x;
+  int b = lane;
+  for (; b + 96 < G; b += 128) {
+    const double a0 = __ldcg(&part[(size_t)b * Kp + c]), a1 = __ldcg(&part[(size_t)(b + 32) * Kp + c]);
+    const double a2 = __ldcg(&part[(size_t)(b + 64) * Kp + c]), a3 = __ldcg(&part[(size_t)(b + 96) * Kp + c]);
+    v0 += a0; v1 += a1; v2 += a2; v3 += a3;
+  }
+  for (; b < G; b += 32) v0 += __ldcg(&part[(size_t)b * Kp + c]);
+  double v = (v0 + v1) + (v2 + v3);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, o);
+  return v;
+}
+
+// CTA b owns the row tiles b, b + gridDim.x, ... (M of them, rows_per_block rows each); `cap` = entries of the largest
+// tile.  Dynamic shared memory: M * cap {col, val} pairs, the block-reduction scratch (blockDim.x * 4 doubles), and
+// per column: rz (two generations), p.r of the replacement, alpha, beta.
+// part: 2 * gridDim.x * Kp doubles (p.Ap partials, then r.z partials).
+template <int M>
+__global__ void __launch_bounds__(256) k_pcg_chunk(int n, int Q, int chunk, int it0, int kstride, int cap,
+                                                   const uint32_t* __restrict__ rowptr, const int* __restrict__ col,
+                                                   const float* __restrict__ val, const float* __restrict__ diag,
+                                                   const float* __restrict__ invd, float4* P, const float4* R,
+                                                   float4* Xd, double* pAp3, double* rz3, const double* rz0,
+                                                   const double* pr_first, const int* frozen, double done_factor,
+                                                   unsigned* bar, double* part, long long* dbg) {
+  extern __shared__ __align__(16) unsigned char chunk_smem[];
+  const int Kp = 4 * Q;
+  int2* ent = (int2*)chunk_smem;                                  // [M][cap] {col, val bits}
+  double* arr = (double*)(chunk_smem + (size_t)M * cap * 8);      // [blockDim.x][4]
+  double* s_rz = arr + blockDim.x * 4;                            // [2][Kp]
+  double* s_pr = s_rz + 2 * Kp;                                   // [Kp]
+  double* s_rz0 = s_pr + Kp;                                      // [Kp] done_factor * rz of the initial residual
+  float* s_al = (float*)(s_rz0 + Kp);                             // [Kp]
+  float* s_be = s_al + Kp;                                        // [Kp]
+  int* s_frozen = (int*)(s_be + Kp);                              // [Kp]
+  double* partA = part;
+  double* partB = part + (size_t)gridDim.x * Kp;
+  long long tk[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tprev = clock64();
+#define TCS_TICK(slot) do { if (dbg) { const long long _t = clock64(); tk[slot] += _t - tprev; tprev = _t; } } while (0)
+  const int rows_per_block = blockDim.x / Q;
+  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const bool active = local < rows_per_block;
+  int row[M], e0[M], e1[M];
+  float4 r[M], xd[M], p[M], ap[M];
+  float dg[M], iv[M];
+  for (int c = threadIdx.x; c < Kp; c += blockDim.x) {
+    s_rz[c] = __ldcg(&rz3[(it0 % 3) * kstride + c]);
+    s_pr[c] = pr_first ? __ldcg(&pr_first[c]) : 0.0;
+    s_rz0[c] = done_factor * __ldcg(&rz0[c]);
+    s_frozen[c] = __ldcg(&frozen[c]);
+  }
+#pragma unroll
+  for (int m = 0; m < M; ++m) {
+    const int tile_row0 = (blockIdx.x + m * gridDim.x) * rows_per_block;
+    row[m] = tile_row0 + local;
+    const bool ok = active && row[m] < n;
+    if (!ok) row[m] = -1;
+    const int tile_row1 = min(n, tile_row0 + rows_per_block);
+    const uint32_t base = tile_row0 < n ? rowptr[tile_row0] : 0u;
+    const uint32_t end = tile_row0 < n ? rowptr[tile_row1] : 0u;
+    for (uint32_t a = base + threadIdx.x; a < end; a += blockDim.x)
+      ent[m * cap + (a - base)] = make_int2(col[a], __float_as_int(val[a]));
+    e0[m] = e1[m] = 0;
+    r[m] = xd[m] = p[m] = ap[m] = make_float4(0.f, 0.f, 0.f, 0.f);
+    dg[m] = iv[m] = 0.f;
+    if (ok) {
+      e0[m] = m * cap + (int)(rowptr[row[m]] - base);
+      e1[m] = m * cap + (int)(rowptr[row[m] + 1] - base);
+      const size_t i = (size_t)row[m] * Q + q;
+      r[m] = R[i]; xd[m] = Xd[i]; p[m] = __ldcg(&P[i]);
+      dg[m] = diag[row[m]]; iv[m] = invd[row[m]];
+    }
+  }
+  __syncthreads();
+  unsigned target = 0;
+  int cur = 0;  // generation of s_rz holding r.z of the current iteration
+  for (int j = 0; j < chunk; ++j) {
+    const bool after_replacement = j == 0 && pr_first != nullptr;
+    // ---- AP = L P, p . Ap
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      if (row[m] < 0) continue;
+      float4 y = make_float4(dg[m] * p[m].x, dg[m] * p[m].y, dg[m] * p[m].z, dg[m] * p[m].w);
+      int a = e0[m];
+      const int a1 = e1[m];
+      // eight gathers in flight (an L2 round trip each); the tail batch is padded with zero-weight reads of the own
+      // row, so the sum keeps CSR order and every load is issued before the first FMA of its batch
+      const size_t own = (size_t)row[m] * Q + q;
+      for (; a < a1; a += 8) {
+        float4 t[8];
+        float w[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const bool in = a + u < a1;
+          const int2 e = in ? ent[a + u] : make_int2(0, 0);
+          w[u] = __int_as_float(e.y);
+          t[u] = __ldcg(&P[in ? (size_t)e.x * Q + q : own]);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (a + u < a1) { y.x += w[u] * t[u].x; y.y += w[u] * t[u].y; y.z += w[u] * t[u].z; y.w += w[u] * t[u].w; }
+        }
+      }
+      ap[m] = y;
+      acc[0] += (double)p[m].x * (double)y.x; acc[1] += (double)p[m].y * (double)y.y;
+      acc[2] += (double)p[m].z * (double)y.z; acc[3] += (double)p[m].w * (double)y.w;
+    }
+    TCS_TICK(0);
+    chunk_block_partials(acc, Q, arr, partA);
+    TCS_TICK(1);
+    grid_barrier(bar, target);
+    TCS_TICK(2);
+    // ---- alpha (pcg_alpha), r -= alpha Ap, r . D^-1 r
+    for (int c = warp; c < Kp; c += nwarps) {
+      const double den = chunk_column_total(partA, Kp, c);
+      if (lane == 0) {
+        const double num = after_replacement ? s_pr[c] : s_rz[cur * Kp + c];
+        const bool live = den > 0.0 && num > s_rz0[c] && !s_frozen[c];
+        const double ratio = live ? num / den : 0.0;
+        s_al[c] = ratio < 1e30 ? (float)ratio : 0.0f;
+      }
+    }
+    __syncthreads();
+    float al[4] = {0.f, 0.f, 0.f, 0.f};
+    acc[0] = acc[1] = acc[2] = acc[3] = 0.0;
+    if (active) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) al[c] = s_al[4 * q + c];
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) {
+      if (row[m] < 0) continue;
+      if (al[0] != 0.f) r[m].x -= al[0] * ap[m].x;
+      if (al[1] != 0.f) r[m].y -= al[1] * ap[m].y;
+      if (al[2] != 0.f) r[m].z -= al[2] * ap[m].z;
+      if (al[3] != 0.f) r[m].w -= al[3] * ap[m].w;
+      const double e = (double)iv[m];
+      acc[0] += (double)r[m].x * (double)r[m].x * e; acc[1] += (double)r[m].y * (double)r[m].y * e;
+      acc[2] += (double)r[m].z * (double)r[m].z * e; acc[3] += (double)r[m].w * (double)r[m].w * e;
+    }
+    TCS_TICK(3);
+    chunk_block_partials(acc, Q, arr, partB);
+    TCS_TICK(4);
+    grid_barrier(bar, target);
+    TCS_TICK(5);
+    // ---- beta, xd += alpha p, p = D^-1 r + beta p
+    for (int c = warp; c < Kp; c += nwarps) {
+      const double num = chunk_column_total(partB, Kp, c);
+      if (lane == 0) {
+        const double den = s_rz[cur * Kp + c];
+        const bool live = den > s_rz0[c] && den > 0.0 && !s_frozen[c] && !(after_replacement && s_pr[c] <= 0.0);
+        const double ratio = live ? num / den : 0.0;
+        s_be[c] = ratio < 1e30 ? (float)ratio : 0.0f;
+        s_rz[(cur ^ 1) * Kp + c] = num;
+      }
+    }
+    __syncthreads();
+    cur ^= 1;
+    if (active) {
+      float be[4];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) be[c] = s_be[4 * q + c];
+#pragma unroll
+      for (int m = 0; m < M; ++m) {
+        if (row[m] < 0) continue;
+        float4 x = xd[m], pv = p[m];
+        const float d = iv[m];
+        if (al[0] != 0.f) x.x += al[0] * pv.x;
+        if (al[1] != 0.f) x.y += al[1] * pv.y;
+        if (al[2] != 0.f) x.z += al[2] * pv.z;
+        if (al[3] != 0.f) x.w += al[3] * pv.w;
+        pv.x = r[m].x * d + (be[0] != 0.f ? be[0] * pv.x : 0.f); pv.y = r[m].y * d + (be[1] != 0.f ? be[1] * pv.y : 0.f);
+        pv.z = r[m].z * d + (be[2] != 0.f ? be[2] * pv.z : 0.f); pv.w = r[m].w * d + (be[3] != 0.f ? be[3] * pv.w : 0.f);
+        xd[m] = x; p[m] = pv;
+        P[(size_t)row[m] * Q + q] = pv;
+      }
+    }
+    TCS_TICK(6);
+    grid_barrier(bar, target);
+    TCS_TICK(7);
+  }
+  // r is not written back: every chunk is followed by the float64 residual replacement, which rewrites R (and r.z).
+  // The global accumulators of the per-kernel path stay cleared.
+#pragma unroll
+  for (int m = 0; m < M; ++m)
+    if (row[m] >= 0) Xd[(size_t)row[m] * Q + q] = xd[m];
+  if (blockIdx.x == 0)
+    for (int i = threadIdx.x; i < 3 * kstride; i += blockDim.x) { pAp3[i] = 0.0; rz3[i] = 0.0; }
+  if (dbg && threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1))
+    for (int i = 0; i < 8; ++i) dbg[(blockIdx.x ? 8 : 0) + i] = tk[i];
+#undef TCS_TICK
+}
+
 // assignColors (impl/random_walker.hpp:209-222): first maximal potential of the row; rows whose potentials are all
 // zero (seedless components, :191-192) stay unlabelled.  Also scatters potentials (getPotentials, :224-243).
 __global__ void k_argmax(int n, int K, int Kp, int k0, int k1, const double* __restrict__ X,
@@ -785,8 +1030,61 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     int* h_frozen = (int*)((char*)ctx->h_pin + 2048);
     for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
     PcgLaunch L = pcg_launch_shape(ctx, n, Qw);
-    TRY(spmm_plan(ctx, S));
-    kernel_at_start = S.ring ? 3 : S.tiled ? 2 : 1;
+    // small systems: whole chunks of iterations in one persistent cooperative launch (k_pcg_chunk) instead of three
+    // launches per iteration; no SpMM plan is needed then (the measurement hooks plan on demand)
+    DBuf<unsigned> coop_bar;
+    DBuf<double> coop_part;     // per-CTA partial dot products
+    DBuf<long long> coop_dbg;   // TCS_DEBUG: cycles per phase of the first and the last CTA
+    TRY(coop_bar.alloc(ctx, 1));
+    if (getenv("TCS_DEBUG")) TRY(coop_dbg.alloc(ctx, 16));
+    unsigned coop_grid = 0;
+    int coop_M = 0, coop_cap = 0;
+    size_t coop_smem = 0;
+    const void* coop_fn = nullptr;
+    auto plan_iteration = [&]() -> int {
+      coop_grid = 0;
+      const int rows_per_block = 256 / Qw;
+      const int ntiles = (n + rows_per_block - 1) / rows_per_block;
+      // at most 4 row tiles per CTA, all CTAs co-resident: n * Q <= ~1.2 M (a 640 x 480 scene with 16 labels is 0.2 M)
+      if (env_int("TCS_COOP", 1) != 0 && !opts.time_spmm && !getenv("TCS_SPMM") && ntiles <= 4 * 8 * ctx->sm_count &&
+          n <= env_int("TCS_COOP_MAX_ROWS", 100000)) {
+        uint32_t* d_max = (uint32_t*)ctx->d_scal + 16;
+        CK(cudaMemsetAsync(d_max, 0, 4, ctx->stream));
+        LAUNCH(ctx, k_tile_max_nnz, div_up(ntiles, 256), 256, 0, n, rows_per_block, S.rowptr.p, d_max);
+        uint32_t mx = 0;
+        TRY(tcs_impl_read_u32(ctx, d_max, &mx));
+        const int cap = (int)((mx + 1u) & ~1u);
+        const void* fns[4] = {(const void*)k_pcg_chunk<1>, (const void*)k_pcg_chunk<2>, (const void*)k_pcg_chunk<3>,
+                              (const void*)k_pcg_chunk<4>};
+        const int max_ctas = env_int("TCS_COOP_CTAS", 8);
+        for (int M = 1; M <= 4; ++M) {
+          const size_t smem = (size_t)M * cap * 8 + 256 * 4 * 8 + (size_t)Kw * (4 * 8 + 3 * 4);
+          if (smem > 200 * 1024) break;
+          if (smem > 48 * 1024 && cudaFuncSetAttribute(fns[M - 1], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+            cudaGetLastError();
+            break;
+          }
+          int nb = 0;
+          if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fns[M - 1], 256, smem) != cudaSuccess || nb < 1) { cudaGetLastError(); break; }
+          const int resident = ctx->sm_count * std::min(nb, max_ctas);
+          const int grid = (ntiles + M - 1) / M;
+          if (grid > resident) continue;
+          coop_grid = (unsigned)grid; coop_M = M; coop_cap = cap; coop_smem = smem; coop_fn = fns[M - 1];
+          TRY(coop_part.alloc(ctx, 2 * (size_t)grid * Kw));
+          S.ring = S.tiled = false;
+          S.plan_stale = true;
+          return TCS_OK;
+        }
+      }
+      return spmm_plan(ctx, S);
+    };
+    {
+      const unsigned sleep_ns = (unsigned)env_int("TCS_COOP_SLEEP", 0);
+      CK(cudaMemcpyToSymbolAsync(c_coop_sleep, &sleep_ns, 4, 0, cudaMemcpyHostToDevice, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+    }
+    TRY(plan_iteration());
+    kernel_at_start = coop_grid ? 4 : S.ring ? 3 : S.tiled ? 2 : 1;
     const float4* B4 = (const float4*)S.B.p;
     float4* P4 = (float4*)S.P.p;
     float4* R4 = (float4*)S.R.p;
@@ -860,7 +1158,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
       S.Kp = Kw;
       compacted = true;
       L = pcg_launch_shape(ctx, n, Qw);
-      TRY(spmm_plan(ctx, S));
+      TRY(plan_iteration());
       B4 = (const float4*)Bw.p; P4 = (float4*)S.P.p; R4 = (float4*)S.R.p; AP4 = (float4*)S.AP.p;
       if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] it=%d: %d columns left, working width %d\n", it, active_cols, Kw);
       phase_report("re-plan");
@@ -887,6 +1185,36 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     }
     while (it < opts.max_iterations) {
       const int chunk = std::min(opts.check_every, opts.max_iterations - it);
+      if (coop_grid) {
+        CK(cudaMemsetAsync(coop_bar.p, 0, 4, ctx->stream));
+        int a_n = n, a_Q = Qw, a_chunk = chunk, a_it = it, a_stride = Kp0, a_cap = coop_cap;
+        const uint32_t* a_rowptr = S.rowptr.p;
+        const int* a_col = S.col.p;
+        const float *a_val = S.val.p, *a_diag = S.diag.p, *a_invd = invd.p;
+        const float4* a_R = R4;
+        float4* a_Xd = (float4*)Xd.p;
+        const double *a_rz0 = d_rz0, *a_pr = it > 0 ? d_pr : nullptr;
+        const int* a_frozen = frozen.p;
+        double a_done = done_factor;
+        unsigned* a_bar = coop_bar.p;
+        long long* a_dbg = coop_dbg.p;
+        double* a_part = coop_part.p;
+        void* args[] = {&a_n, &a_Q, &a_chunk, &a_it, &a_stride, &a_cap, &a_rowptr, &a_col, &a_val, &a_diag, &a_invd, &P4, &a_R,
+                        &a_Xd, &d_pAp, &d_rz, &a_rz0, &a_pr, &a_frozen, &a_done, &a_bar, &a_part, &a_dbg};
+        CK(cudaLaunchCooperativeKernel(coop_fn, dim3(coop_grid), dim3(256), args, coop_smem, ctx->stream));
+        ctx->launches++;
+        if (coop_dbg.p && it == 0) {
+          long long hd[16];
+          CK(cudaMemcpyAsync(hd, coop_dbg.p, sizeof hd, cudaMemcpyDeviceToHost, ctx->stream));
+          CK(cudaStreamSynchronize(ctx->stream));
+          for (int b = 0; b < 2; ++b)
+            fprintf(stderr, "[tcs] k_pcg_chunk<%d> grid %u %s CTA, cycles per iteration: spmm %lld reduce %lld barrier %lld | update %lld reduce %lld barrier %lld | dir %lld barrier %lld\n",
+                    coop_M, coop_grid, b ? "last" : "first", hd[8 * b] / chunk, hd[8 * b + 1] / chunk, hd[8 * b + 2] / chunk, hd[8 * b + 3] / chunk,
+                    hd[8 * b + 4] / chunk, hd[8 * b + 5] / chunk, hd[8 * b + 6] / chunk, hd[8 * b + 7] / chunk);
+        }
+        it += chunk;
+        spmm_launches += chunk;
+      } else
       for (int j = 0; j < chunk; ++j, ++it) {
         const int s0 = it % 3, s1 = (it + 1) % 3, s2 = (it + 2) % 3;
         const double* pr = (j == 0 && it > 0) ? d_pr : nullptr;  // first step after a residual replacement

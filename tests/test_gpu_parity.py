@@ -191,13 +191,18 @@ def test_spmm_kernels_agree(ctx, shape, monkeypatch):
     ctx.upload_cloud(xyz, rgba)
     out = {}
     envs = (("generic", 1, {"TCS_SPMM": "v1"}), ("tiled", 2, {"TCS_SPMM": "tiled"}),
-            ("ring", 3, {"TCS_RING_MIN_TILES": "1"}),
-            ("ring_pad", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_PAD": "1"}),
-            ("ring_s2_nodup", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "2", "TCS_RING_DUP": "0", "TCS_RING_ROWS": "1024"}),
+            ("ring", 3, {"TCS_RING_MIN_TILES": "1", "TCS_COOP": "0"}),
+            ("ring_pad", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_PAD": "1", "TCS_COOP": "0"}),
+            ("ring_s2_nodup", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "2", "TCS_RING_DUP": "0", "TCS_RING_ROWS": "1024",
+                                  "TCS_COOP": "0"}),
             ("ring_s4_small", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "4", "TCS_RING_ROWS": "2048", "TCS_RING_FAR": "8",
-                                  "TCS_RING_DUP": "0"}))
+                                  "TCS_RING_DUP": "0", "TCS_COOP": "0"}),
+            # whole iterations in one persistent launch (the default for small systems; forced here for every size)
+            ("chunk", 4, {"TCS_COOP_MAX_ROWS": "100000000"}),
+            ("chunk_1cta", 4, {"TCS_COOP_MAX_ROWS": "100000000", "TCS_COOP_CTAS": "1"}))
     for name, kid, env in envs:
-        for k in ("TCS_SPMM", "TCS_RING_MIN_TILES", "TCS_RING_S", "TCS_RING_DUP", "TCS_RING_ROWS", "TCS_RING_FAR", "TCS_RING_PAD"):
+        for k in ("TCS_SPMM", "TCS_RING_MIN_TILES", "TCS_RING_S", "TCS_RING_DUP", "TCS_RING_ROWS", "TCS_RING_FAR", "TCS_RING_PAD",
+                  "TCS_COOP", "TCS_COOP_MAX_ROWS", "TCS_COOP_CTAS"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -205,10 +210,13 @@ def test_spmm_kernels_agree(ctx, shape, monkeypatch):
         info = r["info"].as_dict()
         assert r["status"] == capi.OK and info["converged"] and max(info["rel_residual"]) <= 1e-6, name
         g = r["graph"]
-        assert info["spmm_kernel"] == kid, (name, info["spmm_kernel"])
+        if kid == 4 and info["rows"] > 60000:   # may be too many rows for co-resident CTAs: the per-kernel path runs
+            assert info["spmm_kernel"] in (2, 3, 4), (name, info["spmm_kernel"])
+        else:
+            assert info["spmm_kernel"] == kid, (name, info["spmm_kernel"])
         for seed in (1, 2):
             diff, ref, dot, k = g.check_spmm(seed)
-            assert k == kid
+            assert k == kid or kid == 4   # after a chunk solve the hook plans the stand-alone SpMM kernel on demand
             assert diff <= 2e-5 * ref and dot < 1e-6, (name, diff, ref, dot)
         out[name] = r["vertex_colour"].copy()
         g.close()
@@ -227,9 +235,10 @@ def test_column_compaction_is_transparent(ctx, shape, monkeypatch):
     sx, sl, _ = seeds_from_labels(xyz, label, 0, 5)
     ctx.upload_cloud(xyz, rgba)
     out = {}
-    for name, env in (("keep", {"TCS_COMPACT": "0"}), ("compact", {"TCS_COMPACT": "1"}),
-                      ("compact_ring", {"TCS_COMPACT": "1", "TCS_RING_MIN_TILES": "1"})):
-        for k in ("TCS_COMPACT", "TCS_RING_MIN_TILES"):
+    for name, env in (("keep", {"TCS_COMPACT": "0", "TCS_COOP": "0"}), ("compact", {"TCS_COMPACT": "1", "TCS_COOP": "0"}),
+                      ("compact_ring", {"TCS_COMPACT": "1", "TCS_RING_MIN_TILES": "1", "TCS_COOP": "0"}),
+                      ("compact_chunk", {"TCS_COMPACT": "1", "TCS_COOP_MAX_ROWS": "100000000"})):
+        for k in ("TCS_COMPACT", "TCS_RING_MIN_TILES", "TCS_COOP", "TCS_COOP_MAX_ROWS"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -244,7 +253,7 @@ def test_column_compaction_is_transparent(ctx, shape, monkeypatch):
         assert diff <= 2e-5 * ref and dot < 1e-6
         out[name] = (r["vertex_colour"].copy(), pot, info["iterations"])
         g.close()
-    for name in ("compact", "compact_ring"):
+    for name in ("compact", "compact_ring", "compact_chunk"):
         assert np.count_nonzero(out[name][0] != out["keep"][0]) <= max(3, len(out[name][0]) // 1000), name
         assert np.all(np.abs(out[name][1].sum(axis=0) - out["keep"][1].sum(axis=0)) < 5e-2)
         assert out[name][2] <= out["keep"][2] + 50
