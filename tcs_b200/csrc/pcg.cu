@@ -1038,6 +1038,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     TRY(coop_bar.alloc(ctx, 1));
     if (getenv("TCS_DEBUG")) TRY(coop_dbg.alloc(ctx, 16));
     unsigned coop_grid = 0;
+    bool coop_disabled = false;
     int coop_M = 0, coop_cap = 0;
     size_t coop_smem = 0;
     const void* coop_fn = nullptr;
@@ -1046,7 +1047,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
       const int rows_per_block = 256 / Qw;
       const int ntiles = (n + rows_per_block - 1) / rows_per_block;
       // at most 4 row tiles per CTA, all CTAs co-resident: n * Q <= ~1.2 M (a 640 x 480 scene with 16 labels is 0.2 M)
-      if (env_int("TCS_COOP", 1) != 0 && !opts.time_spmm && !getenv("TCS_SPMM") && ntiles <= 4 * 8 * ctx->sm_count &&
+      if (!coop_disabled && env_int("TCS_COOP", 1) != 0 && !opts.time_spmm && !getenv("TCS_SPMM") && ntiles <= 4 * 8 * ctx->sm_count &&
           n <= env_int("TCS_COOP_MAX_ROWS", 100000)) {
         uint32_t* d_max = (uint32_t*)ctx->d_scal + 16;
         CK(cudaMemsetAsync(d_max, 0, 4, ctx->stream));
@@ -1060,7 +1061,8 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         for (int M = 1; M <= 4; ++M) {
           const size_t smem = (size_t)M * cap * 8 + 256 * 4 * 8 + (size_t)Kw * (4 * 8 + 3 * 4);
           if (smem > 200 * 1024) break;
-          if (smem > 48 * 1024 && cudaFuncSetAttribute(fns[M - 1], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+          // always the same value: function attributes are shared by every host thread that drives this device
+          if (cudaFuncSetAttribute(fns[M - 1], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) {
             cudaGetLastError();
             break;
           }
@@ -1070,6 +1072,8 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
           const int grid = (ntiles + M - 1) / M;
           if (grid > resident) continue;
           coop_grid = (unsigned)grid; coop_M = M; coop_cap = cap; coop_smem = smem; coop_fn = fns[M - 1];
+          if (getenv("TCS_DEBUG"))
+            fprintf(stderr, "[tcs] chunk plan: n=%d Q=%d tiles=%d cap=%d M=%d grid=%d smem=%zu occupancy=%d\n", n, Qw, ntiles, cap, M, grid, smem, nb);
           TRY(coop_part.alloc(ctx, 2 * (size_t)grid * Kw));
           S.ring = S.tiled = false;
           S.plan_stale = true;
@@ -1201,7 +1205,18 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         double* a_part = coop_part.p;
         void* args[] = {&a_n, &a_Q, &a_chunk, &a_it, &a_stride, &a_cap, &a_rowptr, &a_col, &a_val, &a_diag, &a_invd, &P4, &a_R,
                         &a_Xd, &d_pAp, &d_rz, &a_rz0, &a_pr, &a_frozen, &a_done, &a_bar, &a_part, &a_dbg};
-        CK(cudaLaunchCooperativeKernel(coop_fn, dim3(coop_grid), dim3(256), args, coop_smem, ctx->stream));
+        const cudaError_t lerr = cudaLaunchCooperativeKernel(coop_fn, dim3(coop_grid), dim3(256), args, coop_smem, ctx->stream);
+        if (lerr == cudaErrorCooperativeLaunchTooLarge || lerr == cudaErrorLaunchOutOfResources) {
+          // the CTAs cannot all be resident right now: this solve continues with one launch per kernel
+          cudaGetLastError();
+          if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] cooperative launch refused (%s): per-kernel path\n", cudaGetErrorString(lerr));
+          // (the refused kernel touched nothing: the accumulators are in the state the per-kernel path expects)
+          coop_grid = 0;
+          coop_disabled = true;
+          TRY(spmm_plan(ctx, S));
+          continue;
+        }
+        CK(lerr);
         ctx->launches++;
         if (coop_dbg.p && it == 0) {
           long long hd[16];
