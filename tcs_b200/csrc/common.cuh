@@ -105,7 +105,8 @@ struct SpmmRing {
   int H;          // halo rows on either side of a tile that are guaranteed to be in the ring
   int S;          // pipeline stages (tiles in flight)
   int ring_rows;  // power of two
-  int dup;        // second copy of the ring shifted by half a 128-byte line (64-byte rows only): conflict-free gathers
+  int dup;        // second copy of the ring, shifted by dup_shift bytes: conflict-free gathers (see ring_pair_choice)
+  int dup_shift;  // 64 for 64-byte rows (the other half of the bank line), 48 for 48-byte rows
   int cap;        // {offset, weight} entries per stage (multiple of 8)
   int farcap;     // far rows per stage
   int nctas;

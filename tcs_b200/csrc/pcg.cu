@@ -770,14 +770,19 @@ int spmm_plan_ring(tcs_ctx* ctx, tcs_system& S) {
   // pads them to a 64-byte pitch in shared memory and runs them like 64-byte rows with one idle lane per row group;
   // a bulk copy cannot pad, and filling the ring with 16-byte cp.async instead costs more (+28 us measured on 64-byte
   // rows) than the conflicts it removes (196 us), so it stays off.
+  // What works for them (TCS_RING_Q3PAIR=1, default): four lanes per row group (one idle), so a quarter warp gathers
+  // exactly two rows, and a second ring copy shifted by 48 bytes: for every pair of row starts one combination of
+  // copies is bank-conflict-free, and the plan picks it per pair of entries (ring_pair_choice).
   const bool pad = Q == 3 && env_int("TCS_RING_PAD", 0);
-  T.Qp = pad ? 4 : Q;
+  const bool q3pair = Q == 3 && !pad && env_int("TCS_RING_Q3PAIR", 1) && env_int("TCS_RING_DUP", 1);
+  T.Qp = (pad || q3pair) ? 4 : Q;
   T.pitch = pad ? 64 : rowbytes;
   T.fill_async = pad ? 1 : 0;
   T.G = std::min(16, 32 / T.Qp);  // 16-byte rows: 16 rows per warp step keep the tile (and its stage buffers) at 256 rows
   T.R = kRingWarps * T.G;
   T.S = std::min(8, std::max(2, env_int("TCS_RING_S", 3)));
-  T.dup = (T.pitch == 64 && env_int("TCS_RING_DUP", 1)) ? 1 : 0;
+  T.dup = ((T.pitch == 64 || q3pair) && env_int("TCS_RING_DUP", 1)) ? 1 : 0;
+  T.dup_shift = q3pair ? 48 : 64;
   const int ntiles = (n + T.R - 1) / T.R;
   // small systems are launch-bound and stay with the other kernels (TCS_RING_MIN_TILES=1 forces the ring, for tests)
   if (ntiles < env_int("TCS_RING_MIN_TILES", 4 * ctx->sm_count)) return TCS_OK;

@@ -92,9 +92,31 @@ __global__ void k_ring_perm(int n, int R, int G, int sort_rows, const uint32_t* 
   }
 }
 
+// Shared-memory placement of one gathered row: the two candidate byte offsets (ring copy 1 / copy 2; equal for a far
+// row or when the ring is not duplicated).
+struct RingCand { int o0, o1; };
+// 16-byte units of the 128-byte bank line a Q-unit row at byte offset `off` covers: [u, u + Q) mod 8
+__device__ __forceinline__ bool ring_rows_collide(int off_a, int off_b, int Q) {
+  if (off_a == off_b) return false;  // same words for the same lane index: a broadcast, not a conflict
+  const int d = ((off_b >> 4) - (off_a >> 4)) & 7;
+  return d < Q || 8 - d < Q;
+}
+// The two row groups of a quarter warp (even / odd position) gather one row each in the same LDS.128: pick the ring
+// copies so that the two rows do not share a bank.  64-byte rows: copy 2 is shifted by 64 bytes, the rows end up in
+// opposite halves of the line.  48-byte rows: copy 2 is shifted by 48 bytes; for every distance of the two row starts
+// one of the four combinations is collision-free.  Returns the combination as (copy of even) | (copy of odd) << 1.
+__device__ __forceinline__ int ring_pair_choice(RingCand a, RingCand b, int Q) {
+  if (!ring_rows_collide(a.o0, b.o0, Q)) return 0;
+  if (!ring_rows_collide(a.o0, b.o1, Q)) return 2;
+  if (!ring_rows_collide(a.o1, b.o0, Q)) return 1;
+  if (!ring_rows_collide(a.o1, b.o1, Q)) return 3;
+  return 0;
+}
+
 // Fills the tile blobs: per tile `entries` 16-bit offsets (shared-memory offset of the gathered row in 16-byte units,
 // 227 KB = 14 528 units) followed by `entries` float weights, at byte 6 * tile_start[t].  cv holds
-// {col | -1 - far slot, weight bits} in CSR order.  One thread per (tile, position).
+// {col | -1 - far slot, weight bits} in CSR order.  One thread per (tile, position); with a duplicated ring a thread
+// also walks the entries of its quarter-warp partner (position ^ 1) to choose the copies of the pair jointly.
 __global__ void k_ring_fill(int n, int Q, SpmmRing T, int ntiles, const uint32_t* __restrict__ rowptr,
                             const unsigned char* __restrict__ meta, const uint32_t* __restrict__ tile_start,
                             const int2* __restrict__ cv, unsigned char* __restrict__ blob) {
@@ -105,7 +127,7 @@ __global__ void k_ring_fill(int n, int Q, SpmmRing T, int ntiles, const uint32_t
   const unsigned char* m = meta + (size_t)t * ring_meta_bytes(T.R);
   const uint32_t entries = ((const uint32_t*)m)[0];
   const uint32_t sl = ((const uint32_t*)m)[4 + ws];
-  const int row = t * T.R + ((const uint16_t*)(m + kRingMetaHdr))[pos];
+  const uint16_t* perm = (const uint16_t*)(m + kRingMetaHdr);
   unsigned char* b = blob + (size_t)tile_start[t] * 6;
   uint16_t* off16 = (uint16_t*)b + (sl & 0xFFFFu) + g;
   float* wout = (float*)(b + (size_t)entries * 2) + (sl & 0xFFFFu) + g;
@@ -113,26 +135,38 @@ __global__ void k_ring_fill(int n, int Q, SpmmRing T, int ntiles, const uint32_t
   const int stage = t % T.S;  // a tile's stage is its global index mod S: independent of the CTA ranges
   const int rowbytes = 16 * Q, pitch = T.pitch, mask = T.ring_rows - 1;
   const int far_base = T.off_stage0 + stage * T.stage_bytes + T.off_far;
-  const int ring2 = T.off_ring + T.ring_bytes + 64;
-  uint32_t a = 0, a1 = 0;
-  int own = T.off_ring;
-  if (row < n) {
-    a = rowptr[row];
-    a1 = rowptr[row + 1];
-    own = ((T.dup && ((row ^ pos) & 1)) ? ring2 : T.off_ring) + (row & mask) * pitch;
-  }
-  for (int k = 0; k < L; ++k, ++a) {
-    int off = own;
-    float w = 0.f;  // padding: zero weight times the row's own (finite) P row
-    if (a < a1) {
-      const int2 e = cv[a];
-      const int c = e.x;
-      w = __int_as_float(e.y);
-      if (c < 0) off = far_base + (-1 - c) * rowbytes;
-      // second ring copy when the neighbour row would land in the other half of the 128-byte line than the one
-      // this row group (position parity) reads: the two groups of a quarter warp never meet
-      else if (T.dup && ((c ^ pos) & 1)) off = ring2 + (c & mask) * pitch;
-      else off = T.off_ring + (c & mask) * pitch;
+  const int ring2 = T.off_ring + T.ring_bytes + T.dup_shift;
+  const bool pairs = T.dup && T.Qp == 4;   // two row groups per quarter warp
+  // candidate placements of entry k of a row (padding: the row's own ring slot with a zero weight)
+  auto cand = [&](int row, uint32_t a, uint32_t a1, int k, float* w) -> RingCand {
+    RingCand c;
+    int col = row;
+    *w = 0.f;
+    if (row >= n) { c.o0 = c.o1 = T.off_ring; return c; }
+    if (a + (uint32_t)k < a1) {
+      const int2 e = cv[a + k];
+      *w = __int_as_float(e.y);
+      col = e.x;
+      if (col < 0) { c.o0 = c.o1 = far_base + (-1 - col) * rowbytes; return c; }
+    }
+    c.o0 = T.off_ring + (col & mask) * pitch;
+    c.o1 = T.dup ? ring2 + (col & mask) * pitch : c.o0;
+    return c;
+  };
+  const int row = t * T.R + perm[pos];
+  const int prow = t * T.R + perm[pos ^ 1];
+  uint32_t a = 0, a1 = 0, pa = 0, pa1 = 0;
+  if (row < n) { a = rowptr[row]; a1 = rowptr[row + 1]; }
+  if (pairs && prow < n) { pa = rowptr[prow]; pa1 = rowptr[prow + 1]; }
+  for (int k = 0; k < L; ++k) {
+    float w, pw;
+    const RingCand mine = cand(row, a, a1, k, &w);
+    int off = mine.o0;
+    if (pairs) {
+      const RingCand other = cand(prow, pa, pa1, k, &pw);
+      const int choice = (pos & 1) ? ring_pair_choice(other, mine, Q) : ring_pair_choice(mine, other, Q);
+      const int my_copy = (pos & 1) ? (choice >> 1) : (choice & 1);
+      off = my_copy ? mine.o1 : mine.o0;
     }
     off16[(size_t)k * T.G] = (uint16_t)(off >> 4);
     wout[(size_t)k * T.G] = w;
@@ -192,7 +226,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
     // Nothing sits behind a dependent global load: tile descriptors are prefetched two tiles ahead into registers.
     const int pid = threadIdx.x - 32 * kRingWarps;
     const int pw = pid >> 5;
-    unsigned char* ring = smem + T.off_ring + (pw == 2 ? T.ring_bytes + 64 : 0);
+    unsigned char* ring = smem + T.off_ring + (pw == 2 ? T.ring_bytes + T.dup_shift : 0);
     // u / Q = umulhi(u, qmagic) for u < 2^29 and Q >= 2 (Q = 1 would need 2^32: handled apart)
     const uint32_t qmagic = Q > 1 ? (uint32_t)((0x100000000ull + (unsigned)Q - 1u) / (unsigned)Q) : 0u;
     int hi_prev = 0;
@@ -245,7 +279,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
           const float4* src = &P[(size_t)x * Q + ch];
           unsigned char* dst = rg0 + (size_t)(x & mask) * pitch + ch * 16u;
           cp_async16(dst, src);
-          if (T.dup) cp_async16(dst + T.ring_bytes + 64, src);
+          if (T.dup) cp_async16(dst + T.ring_bytes + T.dup_shift, src);
         }
         hi_prev = hi;
       }
@@ -267,7 +301,8 @@ __global__ void __launch_bounds__(kRingThreads, 1)
     active = g < T.G && q < Q;
     const int pos = warp * T.G + g;
     const unsigned char* Pq = smem + q * 16;
-    const int own_ring2 = T.off_ring + T.ring_bytes + 64;
+    const int own_ring2 = T.off_ring + T.ring_bytes + T.dup_shift;
+    const bool own_by_parity = T.dup && T.dup_shift == 64;   // 64-byte rows: the own-row read follows the position parity
     const int G = T.G;
     for (int t = t0; t < t1; ++t) {
       mbar_wait(&full[s], kq);
@@ -280,7 +315,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         const int L = (int)(sl >> 16);
         const uint16_t* off_s = (const uint16_t*)(st + T.off_cv) + (sl & 0xFFFFu) + g;
         const float* w_s = (const float*)(st + T.off_cv + entries * 2u) + (sl & 0xFFFFu) + g;
-        const int own = (T.dup && ((row ^ pos) & 1)) ? own_ring2 : T.off_ring;
+        const int own = (own_by_parity && ((row ^ pos) & 1)) ? own_ring2 : T.off_ring;
         const float4 p = *(const float4*)(Pq + own + (row & mask) * pitch);
         const float d = ((const float*)(st + T.off_meta + kRingMetaHdr + 2 * T.R))[lr];
         float4 y = make_float4(d * p.x, d * p.y, d * p.z, d * p.w);

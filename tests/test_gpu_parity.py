@@ -193,6 +193,7 @@ def test_spmm_kernels_agree(ctx, shape, monkeypatch):
     envs = (("generic", 1, {"TCS_SPMM": "v1"}), ("tiled", 2, {"TCS_SPMM": "tiled"}),
             ("ring", 3, {"TCS_RING_MIN_TILES": "1", "TCS_COOP": "0"}),
             ("ring_pad", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_PAD": "1", "TCS_COOP": "0"}),
+            ("ring_q3_plain", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_Q3PAIR": "0", "TCS_COOP": "0"}),
             ("ring_s2_nodup", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "2", "TCS_RING_DUP": "0", "TCS_RING_ROWS": "1024",
                                   "TCS_COOP": "0"}),
             ("ring_s4_small", 3, {"TCS_RING_MIN_TILES": "1", "TCS_RING_S": "4", "TCS_RING_ROWS": "2048", "TCS_RING_FAR": "8",
@@ -202,7 +203,7 @@ def test_spmm_kernels_agree(ctx, shape, monkeypatch):
             ("chunk_1cta", 4, {"TCS_COOP_MAX_ROWS": "100000000", "TCS_COOP_CTAS": "1"}))
     for name, kid, env in envs:
         for k in ("TCS_SPMM", "TCS_RING_MIN_TILES", "TCS_RING_S", "TCS_RING_DUP", "TCS_RING_ROWS", "TCS_RING_FAR", "TCS_RING_PAD",
-                  "TCS_COOP", "TCS_COOP_MAX_ROWS", "TCS_COOP_CTAS"):
+                  "TCS_RING_Q3PAIR", "TCS_COOP", "TCS_COOP_MAX_ROWS", "TCS_COOP_CTAS"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
