@@ -64,7 +64,8 @@ typedef struct tcs_term {
 typedef struct tcs_solver_opts {
   double tolerance;      /* relative residual ||b - Lx|| / ||b|| per label column; default 1e-6 */
   int max_iterations;    /* default 200000 */
-  int check_every;       /* iterations between float64 true-residual replacements / convergence checks; default 50 */
+  int check_every;       /* iterations between float64 true-residual replacements / convergence checks; default 50
+                            (doubled while the slowest column is still more than 30x above the tolerance) */
   int store_potentials;  /* keep the dense V x K potentials on the device (getPotentials) */
   int time_spmm;         /* bracket sampled SpMM launches with CUDA events (fills tcs_solve_info.spmm_ms) */
   /* label-column shard: solve only the colour columns [column_begin, column_begin +

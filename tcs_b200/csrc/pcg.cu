@@ -19,11 +19,28 @@ namespace {
 __device__ __forceinline__ bool is_pow2(int q) { return (q & (q - 1)) == 0; }
 
 // Block-level reduction of per-thread partial sums of 4 columns (column group q of Q) into gout[Kp].
-__device__ __forceinline__ void reduce_columns(double acc[4], int q, int Q, bool active, double* sm, double* gout) {
+// packed = the thread layout of the vector kernels (thread = row * Q + q): the lanes of a warp that hold the same
+// column group sit Q apart also when Q is not a power of two, so they are summed with strided shuffles first
+// (without this a 12-column block makes every thread hit twelve shared-memory words with fp64 CAS loops: 15 us on C4).
+__device__ __forceinline__ void reduce_columns(double acc[4], int q, int Q, bool active, double* sm, double* gout,
+                                               bool packed = false) {
   const int Kp = 4 * Q;
   for (int i = threadIdx.x; i < Kp; i += blockDim.x) sm[i] = 0.0;
   __syncthreads();
-  if (is_pow2(Q) && Q <= 32) {
+  if (packed && !is_pow2(Q) && Q < 32) {
+    const int lane = threadIdx.x & 31;
+    for (int o = Q; o < 32; o <<= 1) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const double v = __shfl_down_sync(0xFFFFFFFFu, acc[j], o);
+        if (lane + o < 32) acc[j] += v;
+      }
+    }
+    if (lane < Q) {   // lane l < Q now holds the sum over lanes l, l + Q, l + 2 Q, ... (all of its column group)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) atomicAdd(&sm[4 * q + j], acc[j]);
+    }
+  } else if (is_pow2(Q) && Q <= 32) {
     for (int o = 16; o >= Q; o >>= 1) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[j] += __shfl_xor_sync(0xFFFFFFFFu, acc[j], o);
@@ -86,7 +103,7 @@ __global__ void __launch_bounds__(256) k_spmm(int n, int Q, const uint32_t* __re
       acc[2] += (double)p.z * (double)y.z; acc[3] += (double)p.w * (double)y.w;
     }
   }
-  reduce_columns(acc, q, Q, active, sm, pAp);
+  reduce_columns(acc, q, Q, active, sm, pAp, true);
 }
 
 // x = 0, r = b, p = D^-1 b, rz = sum b^2 / d, bb = sum b^2 ; also 1/d
@@ -118,9 +135,9 @@ __global__ void __launch_bounds__(256) k_pcg_init(int n, int Q, const float4* __
       a_rz[2] += (double)b.z * b.z * di; a_rz[3] += (double)b.w * b.w * di;
     }
   }
-  reduce_columns(a_rz, q, Q, active, sm, rz);
+  reduce_columns(a_rz, q, Q, active, sm, rz, true);
   __syncthreads();
-  reduce_columns(a_bb, q, Q, active, sm, bb);
+  reduce_columns(a_bb, q, Q, active, sm, bb, true);
 }
 
 // Step length of column c: alpha = r.z / p.Ap, or the exact line search p.r / p.Ap on the iteration after a residual
@@ -191,7 +208,7 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
       acc[2] += (double)r.z * (double)r.z * e; acc[3] += (double)r.w * (double)r.w * e;
     }
   }
-  reduce_columns(acc, q, Q, active, sm, rz_next);
+  reduce_columns(acc, q, Q, active, sm, rz_next, true);
 }
 
 // X += xd ; xd = 0  (before every float64 true residual)
@@ -325,11 +342,11 @@ __global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint3
       a_pr[2] += (double)pv.z * rf.z; a_pr[3] += (double)pv.w * rf.w;
     }
   }
-  reduce_columns(a_rr, q, Q, active, sm, rr);
+  reduce_columns(a_rr, q, Q, active, sm, rr, true);
   __syncthreads();
-  reduce_columns(a_rz, q, Q, active, sm, rz);
+  reduce_columns(a_rz, q, Q, active, sm, rz, true);
   __syncthreads();
-  reduce_columns(a_pr, q, Q, active, sm, pr);
+  reduce_columns(a_pr, q, Q, active, sm, pr, true);
 }
 
 // ---- small systems: `chunk` whole PCG iterations in ONE persistent launch -------------------------------------------
@@ -1192,8 +1209,14 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         CK(cudaStreamSynchronize(ctx->stream));
       }
     }
+    // Every check costs a pass over the float64 solution and a float64 SpMM (8 % of the iterations' time on C4 at one
+    // check per 50 iterations).  While the slowest column is still far from the tolerance - more than a factor
+    // TCS_CHECK_FAR (default 30; 0 = off) above it, i.e. well over a thousand Jacobi-PCG iterations away on these
+    // systems - the next interval is twice check_every.
+    const double far_factor = (double)env_int("TCS_CHECK_FAR", 30);
+    int next_chunk = opts.check_every;
     while (it < opts.max_iterations) {
-      const int chunk = std::min(opts.check_every, opts.max_iterations - it);
+      const int chunk = std::min(next_chunk, opts.max_iterations - it);
       if (coop_grid) {
         CK(cudaMemsetAsync(coop_bar.p, 0, 4, ctx->stream));
         int a_n = n, a_Q = Qw, a_chunk = chunk, a_it = it, a_stride = Kp0, a_cap = coop_cap;
@@ -1275,6 +1298,12 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         fprintf(stderr, "\n");
       }
       if (active_cols == 0) { converged = 1; phase_report("done"); break; }
+      {
+        double worst = 0.0;
+        for (int kw = 0; kw < Kw; ++kw)
+          if (wmap[kw] >= 0 && !done[wmap[kw]]) worst = std::max(worst, rel[wmap[kw]]);
+        next_chunk = (far_factor > 0.0 && worst > far_factor * opts.tolerance) ? 2 * opts.check_every : opts.check_every;
+      }
       const int newKw = std::max(4, (active_cols + 3) & ~3);
       if (compact_enabled && newKw < Kw && it < opts.max_iterations) {
         TRY(compact(newKw, active_cols));
