@@ -135,7 +135,7 @@ def run_reference(args, rank, world):
     print(json.dumps({
         "impl": "reference", "metric": "rw_segmentation_vertices_per_s", "value": val, "unit": "vertices/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps,
-        "higher_is_better": True, "scaling": "strong" if columns else "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
         "cpu_baseline": {"value": val, "unit": "vertices/s", "cores": 1, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "vertices/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
