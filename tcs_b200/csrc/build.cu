@@ -89,12 +89,48 @@ __global__ void k_transform_minmax(const float4* __restrict__ cloud, size_t n, u
   }
 }
 
+// OctreePointCloud::adoptBoundingBoxToPoint (appendix A.2) grows the tree while points are inserted one by one:
+// a point's key is taken with the box that was current at ITS insertion, and every later doubling pushes the old
+// root one level down (the keys inserted so far gain a top bit on the axes that grew downwards).  The host finds the
+// few growth events (k_first_outside) and hands them over as epochs: points [estart[e], estart[e+1]) use emn[e],
+// then OR eor[e] (the top bits of all later doublings).
+#define TCS_MAX_EPOCHS 24
 struct BoxParams {
   double mn[3];
   double res;
   int depth;
   int desc;
+  int nepoch;  // 1 = no growth (mn[] alone is used)
+  uint32_t estart[TCS_MAX_EPOCHS];
+  double emn[TCS_MAX_EPOCHS][3];
+  uint32_t eor[TCS_MAX_EPOCHS][3];
 };
+
+// lowest index >= from of a finite point outside [mn, mx)  (the next point adoptBoundingBoxToPoint would grow for)
+struct BoxD { double mn[3], mx[3]; };
+__global__ void k_first_outside(const float4* __restrict__ cloud, size_t n, size_t from, BoxD b,
+                                uint32_t* __restrict__ out) {
+  uint32_t best = 0xFFFFFFFFu;
+  for (size_t i = from + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    float t[3];
+    if (!transform_point(cloud[i], t[0], t[1], t[2])) continue;
+    bool outside = false;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) outside = outside || (double)t[a] < b.mn[a] || (double)t[a] >= b.mx[a];
+    if (outside) { best = (uint32_t)i; break; }  // indices ascend along the grid-stride loop
+  }
+#pragma unroll
+  for (int s = 16; s > 0; s >>= 1) best = min(best, __shfl_xor_sync(0xFFFFFFFFu, best, s));
+  if ((threadIdx.x & 31) == 0 && best != 0xFFFFFFFFu) atomicMin(out, best);
+}
+
+// transformed coordinates of the point *idx (device-side so that they are the same floats k_sort_keys sees)
+__global__ void k_transformed_point_guarded(const float4* __restrict__ cloud, const uint32_t* __restrict__ idx,
+                                            float* __restrict__ out) {
+  float t[3] = {0.f, 0.f, 0.f};
+  if (*idx != 0xFFFFFFFFu) transform_point(cloud[*idx], t[0], t[1], t[2]);
+  out[0] = t[0]; out[1] = t[1]; out[2] = t[2];
+}
 
 __device__ __forceinline__ uint64_t spread3(uint32_t v) {  // 21 bits -> every third bit
   uint64_t x = v & 0x1FFFFFu;
@@ -127,9 +163,18 @@ __global__ void k_sort_keys(const float4* __restrict__ cloud, size_t n, BoxParam
   const uint64_t sentinel = 1ull << (3 * bp.depth);
   uint64_t k = sentinel;
   if (transform_point(cloud[i], tx, ty, tz)) {
-    uint32_t kx = (uint32_t)(((double)tx - bp.mn[0]) / bp.res);
-    uint32_t ky = (uint32_t)(((double)ty - bp.mn[1]) / bp.res);
-    uint32_t kz = (uint32_t)(((double)tz - bp.mn[2]) / bp.res);
+    uint32_t kx, ky, kz;
+    if (bp.nepoch <= 1) {
+      kx = (uint32_t)(((double)tx - bp.mn[0]) / bp.res);
+      ky = (uint32_t)(((double)ty - bp.mn[1]) / bp.res);
+      kz = (uint32_t)(((double)tz - bp.mn[2]) / bp.res);
+    } else {
+      int e = 0;
+      while (e + 1 < bp.nepoch && i >= bp.estart[e + 1]) ++e;
+      kx = (uint32_t)(((double)tx - bp.emn[e][0]) / bp.res) | bp.eor[e][0];
+      ky = (uint32_t)(((double)ty - bp.emn[e][1]) / bp.res) | bp.eor[e][1];
+      kz = (uint32_t)(((double)tz - bp.emn[e][2]) / bp.res) | bp.eor[e][2];
+    }
     uint64_t m = spread3(kx) << 2 | spread3(ky) << 1 | spread3(kz);
     k = bp.desc ? (~m & (sentinel - 1)) : m;
   }
@@ -309,6 +354,17 @@ struct OctreeBox {
       mx[a] += over;
     }
   }
+  // getKeyBitSize() on a tree that already holds leaves: depth from the current box, max = min + side
+  void refit_nonempty() {
+    const float eps = FLT_EPSILON;
+    unsigned mk[3];
+    for (int a = 0; a < 3; ++a) mk[a] = static_cast<unsigned>((mx[a] - mn[a]) / res);
+    unsigned max_voxels = std::max(std::max(std::max(mk[0], mk[1]), mk[2]), 2u);
+    double l2 = std::log((double)max_voxels) / std::log(2.0);
+    depth = std::max(std::min(64u, static_cast<unsigned>(std::ceil(l2 - eps))), 0u);
+    double side = static_cast<double>(1ull << depth) * res - eps;
+    for (int a = 0; a < 3; ++a) mx[a] = mn[a] + side;
+  }
 };
 
 template <typename KeyT>
@@ -391,13 +447,66 @@ extern "C" int tcs_build_voxel_graph(tcs_ctx* ctx, float resolution, int leaf_or
     box.mx[a] = std::max(lo, hi);
   }
   box.fit();
-  if (box.negative_oversize)
-    // max_voxels an exact power of two: PCL grows the tree point by point (adoptBoundingBoxToPoint).  That
-    // sequential path is not reproduced on the device yet; refuse instead of returning different keys.
-    return fail(tcs_fail(ctx, TCS_ERR_DEPTH, "octree bounding box needs run-time growth (max_voxels is a power of two); unsupported"));
+  BoxParams bp;
+  bp.nepoch = 1;
+  bp.estart[0] = 0;
+  for (int a = 0; a < 3; ++a) { bp.emn[0][a] = box.mn[a]; bp.eor[0][a] = 0; }
+  {
+    // Points outside [min, max) make PCL grow the tree while inserting (adoptBoundingBoxToPoint); this happens when
+    // max_voxels is an exact power of two (the fitted cube is then a hair smaller than the extent).  The extreme
+    // coordinates tell exactly whether any point is outside; if so, replay the growth events in insertion order.
+    bool outside = false;
+    for (int a = 0; a < 3; ++a) {
+      double lo = (double)ord2f(hmm[a]), hi = (double)ord2f(hmm[3 + a]);
+      outside = outside || std::min(lo, hi) < box.mn[a] || std::max(lo, hi) >= box.mx[a];
+    }
+    uint32_t* d_idx = (uint32_t*)ctx->d_scal + 8;
+    float* d_pt = (float*)ctx->d_scal + 9;
+    size_t from = 0;
+    while (outside && from < n) {
+      CKG(cudaMemsetAsync(d_idx, 0xFF, 4, ctx->stream));
+      BoxD bd;
+      for (int a = 0; a < 3; ++a) { bd.mn[a] = box.mn[a]; bd.mx[a] = box.mx[a]; }
+      unsigned gr = std::min<unsigned>(div_up(n - from, 256), (unsigned)ctx->sm_count * 8);
+      LAUNCH(ctx, k_first_outside, gr, 256, 0, ctx->d_cloud, n, from, bd, d_idx);
+      LAUNCH(ctx, k_transformed_point_guarded, 1, 1, 0, ctx->d_cloud, d_idx, d_pt);
+      CKG(cudaMemcpyAsync(ctx->h_pin, d_idx, 16, cudaMemcpyDeviceToHost, ctx->stream));
+      CKG(cudaStreamSynchronize(ctx->stream));
+      uint32_t idx;
+      float pf[3];
+      memcpy(&idx, ctx->h_pin, 4);
+      memcpy(pf, (char*)ctx->h_pin + 4, 12);
+      if (idx == 0xFFFFFFFFu) break;
+      const double p[3] = {(double)pf[0], (double)pf[1], (double)pf[2]};
+      if (bp.nepoch >= TCS_MAX_EPOCHS)
+        return fail(tcs_fail(ctx, TCS_ERR_DEPTH, "octree grew more than %d times", TCS_MAX_EPOCHS - 1));
+      for (;;) {
+        bool up[3], any = false;
+        for (int a = 0; a < 3; ++a) {
+          up[a] = p[a] >= box.mx[a];
+          any = any || up[a] || p[a] < box.mn[a];
+        }
+        if (!any) break;
+        if (box.depth >= 31) return fail(tcs_fail(ctx, TCS_ERR_DEPTH, "octree depth exceeds 31 while growing"));
+        // the old root becomes child ((!upX)<<2 | (!upY)<<1 | !upZ) of the new root
+        const uint32_t bit = 1u << box.depth;
+        for (int e = 0; e < bp.nepoch; ++e)
+          for (int a = 0; a < 3; ++a) if (!up[a]) bp.eor[e][a] |= bit;
+        double side = static_cast<double>(1ull << box.depth) * box.res;
+        for (int a = 0; a < 3; ++a) if (!up[a]) box.mn[a] -= side;
+        box.depth++;
+        side = static_cast<double>(1ull << box.depth) * box.res - FLT_EPSILON;
+        for (int a = 0; a < 3; ++a) box.mx[a] = box.mn[a] + side;
+        box.refit_nonempty();
+      }
+      const int e = bp.nepoch++;
+      bp.estart[e] = idx;
+      for (int a = 0; a < 3; ++a) { bp.emn[e][a] = box.mn[a]; bp.eor[e][a] = 0; }
+      from = (size_t)idx + 1;
+    }
+  }
   if (box.depth > 21 || box.depth == 0) return fail(tcs_fail(ctx, TCS_ERR_DEPTH, "octree depth %u outside 1..21", box.depth));
   g->depth = (int)box.depth;
-  BoxParams bp;
   for (int a = 0; a < 3; ++a) { bp.mn[a] = box.mn[a]; g->bbmin[a] = box.mn[a]; }
   bp.res = box.res;
   bp.depth = (int)box.depth;

@@ -126,6 +126,39 @@ def test_single_voxel_cloud(ctx):
     g.close()
 
 
+def _pow2_cloud(seed, n=4000, cells=64, res=0.01, axes=(0,)):
+    """Transformed extent / resolution in [2^d, 2^d + 1) on the given axes: the fitted octree cube is a hair
+    smaller than the extent, so PCL grows the tree while inserting (OctreePointCloud::adoptBoundingBoxToPoint)."""
+    rng = np.random.default_rng(seed)
+    xyz = np.ones((n, 3), np.float32)                       # z = 1: x/z = x, y/z = y, log z = 0
+    xyz[:, :2] = rng.uniform(0.0, 0.2, (n, 2)).astype(np.float32)
+    for a in axes:
+        xyz[:, a] = rng.uniform(0.0, (cells + 0.5) * res, n).astype(np.float32)
+        xyz[rng.integers(n // 2, n), a] = np.float32((cells + 0.5) * res)   # the extremes arrive late
+        xyz[rng.integers(n // 2, n), a] = 0.0
+    xyz[rng.integers(0, n, 20)] = np.nan
+    return xyz, rng.integers(0, 1 << 24, n).astype(np.uint32) | np.uint32(0xFF000000)
+
+
+@pytest.mark.parametrize("seed,axes", [(1, (0,)), (2, (1,)), (3, (0, 1)), (4, (0,)), (5, (0, 1))])
+def test_octree_growth_while_inserting_matches_oracle(ctx, seed, axes):
+    """max_voxels an exact power of two: keys are taken with the box current at each point's insertion and shifted
+    by every later doubling; vertex sets, order, adjacency and the point map must stay bit-exact."""
+    xyz, rgba = _pow2_cloud(seed, axes=axes)
+    o = orc.Graph.from_cloud(xyz, rgba, 0.01)
+    ctx.upload_cloud(xyz, rgba)
+    g = ctx.build_voxel_graph(0.01)
+    assert o.status == 0 and o.depth > 6 and g.depth == o.depth   # grew from the fitted 6 levels, once or more
+    assert (g.V, g.E) == (o.V, o.E)
+    assert np.array_equal(g.keys(), o.keys())
+    assert np.array_equal(g.point_to_vertex(), o.point_to_vertex())
+    for a, b in zip(g.csr(), o.csr()):
+        assert np.array_equal(a, b)
+    for a, b in zip(g.vertices(), o.vertices()):
+        assert np.array_equal(a, b, equal_nan=True) if a.dtype.kind == "f" else np.array_equal(a, b)
+    g.close()
+
+
 def test_cloud_without_colour_matches_oracle(ctx, scenes):
     """PointXYZ input: the RGB term is dropped (EdgeWeightComputer::addTerm on a colourless point type)."""
     sc = scenes["test13"]
