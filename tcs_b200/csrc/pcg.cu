@@ -61,6 +61,7 @@ __device__ __forceinline__ void reduce_columns(double acc[4], int q, int Q, bool
 }  // namespace
 #include "spmm.cuh"
 #include "spmm_ring.cuh"
+#include "coarse.cuh"
 namespace {
 
 // ---- the CG SpMM: AP = L P over all label columns, fused p.Ap partial dots -------------------------------------
@@ -250,7 +251,9 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
                                                  const double* __restrict__ rz_next, double* __restrict__ clear_a,
                                                  double* __restrict__ clear_b, const int* __restrict__ frozen,
                                                  const double* __restrict__ rz0, double done_factor,
-                                                 const double* __restrict__ pr) {
+                                                 const double* __restrict__ pr, const uint32_t* __restrict__ agg,
+                                                 const float4* __restrict__ yc) {
+  // agg / yc: second preconditioner level (coarse.cuh), z = D^-1 r + Z y; NULL = Jacobi alone
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
   if (blockIdx.x == 0)
@@ -273,15 +276,17 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
     const float4 r0 = R[i0], r1 = R[i1];
     float4 p0 = P[i0], p1 = P[i1], x0 = Xd[i0], x1 = Xd[i1];
     const float d0 = invd[row], d1 = invd[row + stride];
+    float4 c0 = make_float4(0.f, 0.f, 0.f, 0.f), c1 = c0;
+    if (agg) { c0 = yc[(size_t)agg[row] * Q + q]; c1 = yc[(size_t)agg[row + stride] * Q + q]; }
     // alpha == 0 / beta == 0 never touch the old p (which may hold inf / nan on a dead column)
     if (al[0] != 0.f) { x0.x += al[0] * p0.x; x1.x += al[0] * p1.x; }
     if (al[1] != 0.f) { x0.y += al[1] * p0.y; x1.y += al[1] * p1.y; }
     if (al[2] != 0.f) { x0.z += al[2] * p0.z; x1.z += al[2] * p1.z; }
     if (al[3] != 0.f) { x0.w += al[3] * p0.w; x1.w += al[3] * p1.w; }
-    p0.x = r0.x * d0 + (be[0] != 0.f ? be[0] * p0.x : 0.f); p0.y = r0.y * d0 + (be[1] != 0.f ? be[1] * p0.y : 0.f);
-    p0.z = r0.z * d0 + (be[2] != 0.f ? be[2] * p0.z : 0.f); p0.w = r0.w * d0 + (be[3] != 0.f ? be[3] * p0.w : 0.f);
-    p1.x = r1.x * d1 + (be[0] != 0.f ? be[0] * p1.x : 0.f); p1.y = r1.y * d1 + (be[1] != 0.f ? be[1] * p1.y : 0.f);
-    p1.z = r1.z * d1 + (be[2] != 0.f ? be[2] * p1.z : 0.f); p1.w = r1.w * d1 + (be[3] != 0.f ? be[3] * p1.w : 0.f);
+    p0.x = r0.x * d0 + c0.x + (be[0] != 0.f ? be[0] * p0.x : 0.f); p0.y = r0.y * d0 + c0.y + (be[1] != 0.f ? be[1] * p0.y : 0.f);
+    p0.z = r0.z * d0 + c0.z + (be[2] != 0.f ? be[2] * p0.z : 0.f); p0.w = r0.w * d0 + c0.w + (be[3] != 0.f ? be[3] * p0.w : 0.f);
+    p1.x = r1.x * d1 + c1.x + (be[0] != 0.f ? be[0] * p1.x : 0.f); p1.y = r1.y * d1 + c1.y + (be[1] != 0.f ? be[1] * p1.y : 0.f);
+    p1.z = r1.z * d1 + c1.z + (be[2] != 0.f ? be[2] * p1.z : 0.f); p1.w = r1.w * d1 + c1.w + (be[3] != 0.f ? be[3] * p1.w : 0.f);
     P[i0] = p0; P[i1] = p1; Xd[i0] = x0; Xd[i1] = x1;
   }
   for (; row < n; row += stride) {
@@ -289,12 +294,14 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
     const float4 r = R[i];
     float4 p = P[i], x = Xd[i];
     const float d = invd[row];
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (agg) c = yc[(size_t)agg[row] * Q + q];
     if (al[0] != 0.f) x.x += al[0] * p.x;
     if (al[1] != 0.f) x.y += al[1] * p.y;
     if (al[2] != 0.f) x.z += al[2] * p.z;
     if (al[3] != 0.f) x.w += al[3] * p.w;
-    p.x = r.x * d + (be[0] != 0.f ? be[0] * p.x : 0.f); p.y = r.y * d + (be[1] != 0.f ? be[1] * p.y : 0.f);
-    p.z = r.z * d + (be[2] != 0.f ? be[2] * p.z : 0.f); p.w = r.w * d + (be[3] != 0.f ? be[3] * p.w : 0.f);
+    p.x = r.x * d + c.x + (be[0] != 0.f ? be[0] * p.x : 0.f); p.y = r.y * d + c.y + (be[1] != 0.f ? be[1] * p.y : 0.f);
+    p.z = r.z * d + c.z + (be[2] != 0.f ? be[2] * p.z : 0.f); p.w = r.w * d + c.w + (be[3] != 0.f ? be[3] * p.w : 0.f);
     P[i] = p; Xd[i] = x;
   }
 }
@@ -1110,12 +1117,20 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
       CK(cudaStreamSynchronize(ctx->stream));
     }
     TRY(plan_iteration());
+    // second preconditioner level (coarse.cuh): large systems on the per-kernel path only
+    coarse::Level CL;
+    if (!coop_grid) TRY(coarse::setup(ctx, S, Kp0, CL));
+    if (CL.on) coop_disabled = true;
     kernel_at_start = coop_grid ? 4 : S.ring ? 3 : S.tiled ? 2 : 1;
     const float4* B4 = (const float4*)S.B.p;
     float4* P4 = (float4*)S.P.p;
     float4* R4 = (float4*)S.R.p;
     float4* AP4 = (float4*)S.AP.p;
     LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Qw, B4, S.diag.p, invd.p, R4, P4, Xw.p, (float4*)Xd.p, d_rz, d_bb);
+    if (CL.on) {
+      TRY(coarse::apply(ctx, CL, Qw, R4, d_rz));
+      LAUNCH(ctx, coarse::k_add_coarse_p, div_up((size_t)n * Qw, 256), 256, 0, n, Qw, P4, CL.agg.p, (const float4*)CL.y.p);
+    }
     CK(cudaMemcpyAsync(d_rz0, d_rz, (size_t)Kp0 * 8, cudaMemcpyDeviceToDevice, ctx->stream));
     std::vector<double> h((size_t)kScalRows * Kp0);
     // sampled SpMM timing: one event pair per launch for the first launches (full width)
@@ -1268,8 +1283,10 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
         ++spmm_launches;
         LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
                d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr);
+        if (CL.on) TRY(coarse::apply(ctx, CL, Qw, R4, d_rz + s1 * Kp0));
         LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
-               d_pAp + s0 * Kp0, d_rz + s1 * Kp0, d_pAp + s1 * Kp0, d_rz + s2 * Kp0, frozen.p, d_rz0, done_factor, pr);
+               d_pAp + s0 * Kp0, d_rz + s1 * Kp0, d_pAp + s1 * Kp0, d_rz + s2 * Kp0, frozen.p, d_rz0, done_factor, pr,
+               CL.on ? CL.agg.p : (const uint32_t*)nullptr, CL.on ? (const float4*)CL.y.p : (const float4*)nullptr);
       }
       // fold the float32 increment into the float64 solution; the float64 true residual replaces the recurrence
       // residual, and rz of the coming iteration is recomputed from it
@@ -1280,6 +1297,7 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
       CK(cudaMemsetAsync(d_pr, 0, (size_t)Kp0 * 8, ctx->stream));
       LAUNCH(ctx, k_true_residual, L.grid, L.block, L.smem, n, Qw, S.rowptr.p, S.col.p, S.val.p, S.diag.p, B4, Xw.p, P4, R4,
              d_rr, d_rz + (it % 3) * Kp0, d_pr);
+      if (CL.on) TRY(coarse::apply(ctx, CL, Qw, R4, d_rz + (it % 3) * Kp0));
       CK(cudaMemcpyAsync(ctx->h_pin, d_rr, (size_t)2 * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
       CK(cudaStreamSynchronize(ctx->stream));
       memcpy(h.data(), ctx->h_pin, (size_t)2 * Kp0 * 8);
