@@ -306,7 +306,9 @@ def run_ours(args, rank, local_rank, world):
             "config": dict(workload_config(args, 1 if columns else world), shard="label columns of one scene, one NCCL "
                            "all-gather per step" if columns else "independent scenes, no collective", vertices=int(V // args.steps), edges=int(E), rows=nrows, nnz=nnz,
                            labels=K_total, pcg_iterations_per_step=iters // args.steps, converged=converged,
-                           max_rel_residual=max(info["rel_residual"])),
+                           max_rel_residual=max(info["rel_residual"]),
+                           preconditioner="Jacobi" if os.environ.get("TCS_COARSE") == "0" else
+                           "Jacobi + strong-edge aggregate coarse level (additive two-level)"),
             "e2e": {"value": Ve_all / (ms_e2e_max * 1e-3), "unit": "vertices/s", "h2d_bytes_per_step": 16 * n + 16 * len(sl),
                     "d2h_bytes_per_step": 4 * n + 4 * int(Ve // args.steps), "ms_per_step": ms_e2e_max / args.steps},
             "gpu_launches": int(launches_all),

@@ -18,6 +18,7 @@
 #include <cusolverDn.h>
 
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -145,18 +146,28 @@ __global__ void __launch_bounds__(256) k_restrict(int n, int Q, int blk, const f
   if (local < rows_per) {
     int cur = -1;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int r = local; r < rows; r += rows_per) {
-      const int a = (int)(agg[row0 + r] - f0);
-      const float4 v = R[(size_t)(row0 + r) * Q + q];
-      if (a != cur) {
-        if (cur >= 0) {
-          float* d = acc + (size_t)cur * W + 4 * q;
-          atomicAdd(d + 0, s.x); atomicAdd(d + 1, s.y); atomicAdd(d + 2, s.z); atomicAdd(d + 3, s.w);
-        }
-        cur = a;
-        s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r0 = local; r0 < rows; r0 += 4 * rows_per) {
+      int a4[4];
+      float4 v4[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {  // four rows in flight
+        const int r = r0 + u * rows_per;
+        a4[u] = r < rows ? (int)(agg[row0 + r] - f0) : -1;
+        v4[u] = r < rows ? R[(size_t)(row0 + r) * Q + q] : make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (a4[u] < 0) continue;
+        if (a4[u] != cur) {
+          if (cur >= 0) {
+            float* d = acc + (size_t)cur * W + 4 * q;
+            atomicAdd(d + 0, s.x); atomicAdd(d + 1, s.y); atomicAdd(d + 2, s.z); atomicAdd(d + 3, s.w);
+          }
+          cur = a4[u];
+          s = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        s.x += v4[u].x; s.y += v4[u].y; s.z += v4[u].z; s.w += v4[u].w;
+      }
     }
     if (cur >= 0) {
       float* d = acc + (size_t)cur * W + 4 * q;
@@ -187,13 +198,34 @@ __global__ void __launch_bounds__(256) k_coarse_gemm(int m, int Q, int b_per_par
   for (int i = 0; i < 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int b0 = b_begin; b0 < b_end; b0 += TCS_COARSE_TB) {
     const int nb = min(TCS_COARSE_TB, b_end - b0);
-    for (int t = threadIdx.x; t < TCS_COARSE_TB * TA; t += blockDim.x) {
-      const int bb = t / TA, a = t - bb * TA;
-      Es[t] = (bb < nb && a0 + a < m) ? Einv[(size_t)(b0 + bb) * m + a0 + a] : 0.f;
+    // eight independent loads in flight per thread (the tile loop has a run-time trip count: without the explicit
+    // batches every load waits for the shared-memory store of the one before)
+    for (int t0 = threadIdx.x; t0 < TCS_COARSE_TB * TA; t0 += 8 * blockDim.x) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int t = t0 + u * blockDim.x;
+        const int bb = t / TA, a = t - bb * TA;
+        v[u] = (t < TCS_COARSE_TB * TA && bb < nb && a0 + a < m) ? Einv[(size_t)(b0 + bb) * m + a0 + a] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int t = t0 + u * blockDim.x;
+        if (t < TCS_COARSE_TB * TA) Es[t] = v[u];
+      }
     }
-    for (int t = threadIdx.x; t < TCS_COARSE_TB * W; t += blockDim.x) {
-      const int bb = t / W;
-      Rs[t] = bb < nb ? rc[(size_t)b0 * W + t] : 0.f;
+    for (int t0 = threadIdx.x; t0 < TCS_COARSE_TB * W; t0 += 4 * blockDim.x) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + u * blockDim.x;
+        v[u] = (t < TCS_COARSE_TB * W && t / W < nb) ? rc[(size_t)b0 * W + t] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int t = t0 + u * blockDim.x;
+        if (t < TCS_COARSE_TB * W) Rs[t] = v[u];
+      }
     }
     __syncthreads();
     if (local < rows_per) {
@@ -308,7 +340,7 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Level& Lv) {
 
   // ---- aggregates = (block of rows, component), numbered block-major
   int blk = env_i("TCS_COARSE_BLOCK", 0);
-  if (blk <= 0) { blk = 256; while (blk < 4096 && (long long)blk * 3000 < n) blk <<= 1; }
+  if (blk <= 0) { blk = 256; while (blk < 4096 && (long long)blk * 1500 < n) blk <<= 1; }
   DBuf<uint64_t> k0, k1;
   DBuf<uint32_t> i0, i1, flag, scan;
   TRY(k0.alloc(ctx, n)); TRY(k1.alloc(ctx, n)); TRY(i0.alloc(ctx, n)); TRY(i1.alloc(ctx, n));
@@ -359,21 +391,29 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Level& Lv) {
   CK(cudaMemsetAsync(dsum.p, 0, (size_t)m * 8, ctx->stream));
   LAUNCH(ctx, k_assemble_E, div_up(n, 256), 256, 0, n, (int)m, S.rowptr.p, S.col.p, S.val.p, S.diag.p, Lv.agg.p, E.p, dsum.p);
   LAUNCH(ctx, k_regularise, div_up(m, 256), 256, 0, (int)m, E.p, dsum.p, env_double("TCS_COARSE_EPS", 1e-8));
-  cusolverDnHandle_t h = nullptr;
-  bool ok = cusolverDnCreate(&h) == CUSOLVER_STATUS_SUCCESS && cusolverDnSetStream(h, ctx->stream) == CUSOLVER_STATUS_SUCCESS;
-  int lw1 = 0, lw2 = 0;
-  ok = ok && cusolverDnDpotrf_bufferSize(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, &lw1) == CUSOLVER_STATUS_SUCCESS;
-  ok = ok && cusolverDnDpotri_bufferSize(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, &lw2) == CUSOLVER_STATUS_SUCCESS;
+  // one cuSOLVER handle per device for the life of the process (creating one costs tens of milliseconds and device
+  // memory); the mutex covers enqueue + synchronise, the handle's workspace is not shared between streams in flight
+  static std::mutex mu;
+  static cusolverDnHandle_t handles[64] = {};
   int hinfo[2] = {-1, -1};
+  bool ok = ctx->device >= 0 && ctx->device < 64;
   if (ok) {
-    TRY(work.alloc(ctx, (size_t)std::max(lw1, lw2) + 1));
-    ok = cusolverDnDpotrf(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, work.p, lw1, info.p) == CUSOLVER_STATUS_SUCCESS;
-    ok = ok && cusolverDnDpotri(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, work.p, lw2, info.p + 1) == CUSOLVER_STATUS_SUCCESS;
-    CK(cudaMemcpyAsync(ctx->h_pin, info.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    memcpy(hinfo, ctx->h_pin, 8);
+    std::lock_guard<std::mutex> lock(mu);
+    cusolverDnHandle_t& h = handles[ctx->device];
+    if (!h && cusolverDnCreate(&h) != CUSOLVER_STATUS_SUCCESS) { h = nullptr; ok = false; }
+    ok = ok && cusolverDnSetStream(h, ctx->stream) == CUSOLVER_STATUS_SUCCESS;
+    int lw1 = 0, lw2 = 0;
+    ok = ok && cusolverDnDpotrf_bufferSize(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, &lw1) == CUSOLVER_STATUS_SUCCESS;
+    ok = ok && cusolverDnDpotri_bufferSize(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, &lw2) == CUSOLVER_STATUS_SUCCESS;
+    if (ok) {
+      TRY(work.alloc(ctx, (size_t)std::max(lw1, lw2) + 1));
+      ok = cusolverDnDpotrf(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, work.p, lw1, info.p) == CUSOLVER_STATUS_SUCCESS;
+      ok = ok && cusolverDnDpotri(h, CUBLAS_FILL_MODE_LOWER, (int)m, E.p, (int)m, work.p, lw2, info.p + 1) == CUSOLVER_STATUS_SUCCESS;
+      CK(cudaMemcpyAsync(ctx->h_pin, info.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+      memcpy(hinfo, ctx->h_pin, 8);
+    }
   }
-  if (h) cusolverDnDestroy(h);
   if (!ok || hinfo[0] != 0 || hinfo[1] != 0) {
     if (dbg) fprintf(stderr, "[tcs] coarse level off: factorisation failed (potrf %d, potri %d)\n", hinfo[0], hinfo[1]);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
