@@ -31,7 +31,8 @@ struct Level {
   size_t restrict_smem = 0;
   DBuf<uint32_t> agg;    // n: aggregate of every row
   DBuf<uint32_t> first;  // nblk + 1: first aggregate id of every block of `blk` rows (ids are contiguous per block)
-  DBuf<float> Einv;      // m x m
+  DBuf<float> Einv;      // m x ld (ld = m rounded up to a multiple of 4, zero padded)
+  int ld = 0;
   DBuf<float> rc, y;     // m x Kp0: Z^T r and E^-1 Z^T r
   float setup_ms = 0.f;
 };
@@ -121,11 +122,12 @@ __global__ void k_regularise(int m, double* __restrict__ E, const double* __rest
 }
 
 // potri leaves the inverse in one triangle (column-major lower = row-major upper): expand to a full float32 matrix
-__global__ void k_einv_f32(int m, const double* __restrict__ Ed, float* __restrict__ Ef) {
+// (rows of ld = m rounded up to 4 floats, zero padded: the product kernel reads them with 16-byte loads)
+__global__ void k_einv_f32(int m, int ld, const double* __restrict__ Ed, float* __restrict__ Ef) {
   size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-  if (t >= (size_t)m * m) return;
-  const int a = (int)(t / m), b = (int)(t - (size_t)a * m);
-  Ef[t] = (float)Ed[(size_t)min(a, b) * m + max(a, b)];
+  if (t >= (size_t)m * ld) return;
+  const int a = (int)(t / ld), b = (int)(t - (size_t)a * ld);
+  Ef[t] = b < m ? (float)Ed[(size_t)min(a, b) * m + max(a, b)] : 0.f;
 }
 
 // rc = Z^T R: one CTA per block of `blk` rows.  A thread keeps one column group and walks rows local, local + rows_per,
@@ -133,7 +135,7 @@ __global__ void k_einv_f32(int m, const double* __restrict__ Ed, float* __restri
 // only flushes a finished run into the shared-memory segment sums.
 __global__ void __launch_bounds__(256) k_restrict(int n, int Q, int blk, const float4* __restrict__ R,
                                                   const uint32_t* __restrict__ agg, const uint32_t* __restrict__ first,
-                                                  float* __restrict__ rc) {
+                                                  float* __restrict__ rc, float* __restrict__ y) {
   extern __shared__ float acc[];
   const int b = blockIdx.x, W = 4 * Q;
   const uint32_t f0 = first[b];
@@ -146,17 +148,17 @@ __global__ void __launch_bounds__(256) k_restrict(int n, int Q, int blk, const f
   if (local < rows_per) {
     int cur = -1;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int r0 = local; r0 < rows; r0 += 4 * rows_per) {
-      int a4[4];
-      float4 v4[4];
+    for (int r0 = local; r0 < rows; r0 += 8 * rows_per) {
+      int a4[8];
+      float4 v4[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {  // four rows in flight
+      for (int u = 0; u < 8; ++u) {  // eight rows in flight
         const int r = r0 + u * rows_per;
         a4[u] = r < rows ? (int)(agg[row0 + r] - f0) : -1;
         v4[u] = r < rows ? R[(size_t)(row0 + r) * Q + q] : make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 8; ++u) {
         if (a4[u] < 0) continue;
         if (a4[u] != cur) {
           if (cur >= 0) {
@@ -175,7 +177,8 @@ __global__ void __launch_bounds__(256) k_restrict(int n, int Q, int blk, const f
     }
   }
   __syncthreads();
-  for (int t = threadIdx.x; t < na * W; t += blockDim.x) rc[(size_t)f0 * W + t] = acc[t];
+  // y of the block's aggregates is cleared here: k_coarse_gemm adds its partial products into it
+  for (int t = threadIdx.x; t < na * W; t += blockDim.x) { rc[(size_t)f0 * W + t] = acc[t]; y[(size_t)f0 * W + t] = 0.f; }
 }
 
 // y += E^-1[:, b-range] rc[b-range]  (dense m x m by m x 4Q product, split over the b range: grid.y parts add their
@@ -183,14 +186,18 @@ __global__ void __launch_bounds__(256) k_restrict(int n, int Q, int blk, const f
 // registers.  E^-1 is symmetric, so the tile E^-1[a-range][b] is read as E^-1[b][a-range]: coalesced, and already in
 // the [b][a] order the float4 shared-memory reads want.
 #define TCS_COARSE_TB 32
-__global__ void __launch_bounds__(256) k_coarse_gemm(int m, int Q, int b_per_part, const float* __restrict__ Einv,
-                                                     const float* __restrict__ rc, float* __restrict__ y) {
+__global__ void __launch_bounds__(256) k_coarse_gemm(int m, int ld, int Q, int rows_per, int b_per_part,
+                                                     const float* __restrict__ Einv, const float* __restrict__ rc,
+                                                     float* __restrict__ y) {
   extern __shared__ float4 sm4[];
-  const int rows_per = blockDim.x / Q;            // thread groups of Q; each group owns 4 aggregates
-  const int TA = 4 * rows_per, W = 4 * Q;
+  // thread = (ks, local, q): group `local` owns 4 aggregates, q a column group, and the KS = blockDim / (rows_per Q)
+  // copies of that layout share the b values of a tile (narrow working sets would otherwise leave a CTA one warp)
+  const int TA = 4 * rows_per, W = 4 * Q, G = rows_per * Q;
+  const int KS = blockDim.x / G;
   float* Es = (float*)sm4;                        // [TB][TA]
   float* Rs = Es + TCS_COARSE_TB * TA;            // [TB][W]
-  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  const int ks = threadIdx.x / G, g = threadIdx.x - ks * G;
+  const int local = g / Q, q = g - local * Q;
   const int a0 = blockIdx.x * TA;
   const int b_begin = blockIdx.y * b_per_part, b_end = min(m, b_begin + b_per_part);
   float4 acc[4];
@@ -198,39 +205,28 @@ __global__ void __launch_bounds__(256) k_coarse_gemm(int m, int Q, int b_per_par
   for (int i = 0; i < 4; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int b0 = b_begin; b0 < b_end; b0 += TCS_COARSE_TB) {
     const int nb = min(TCS_COARSE_TB, b_end - b0);
-    // eight independent loads in flight per thread (the tile loop has a run-time trip count: without the explicit
-    // batches every load waits for the shared-memory store of the one before)
-    for (int t0 = threadIdx.x; t0 < TCS_COARSE_TB * TA; t0 += 8 * blockDim.x) {
-      float v[8];
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int t = t0 + u * blockDim.x;
-        const int bb = t / TA, a = t - bb * TA;
-        v[u] = (t < TCS_COARSE_TB * TA && bb < nb && a0 + a < m) ? Einv[(size_t)(b0 + bb) * m + a0 + a] : 0.f;
-      }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int t = t0 + u * blockDim.x;
-        if (t < TCS_COARSE_TB * TA) Es[t] = v[u];
-      }
-    }
-    for (int t0 = threadIdx.x; t0 < TCS_COARSE_TB * W; t0 += 4 * blockDim.x) {
-      float v[4];
+    // 16-byte loads, up to four in flight per thread (the tile loop has a run-time trip count: without the explicit
+    // batches every load waits for the shared-memory store of the one before).  a0 and ld are multiples of 4.
+    const int TA4 = TA / 4;
+    for (int t0 = threadIdx.x; t0 < TCS_COARSE_TB * TA4; t0 += 4 * blockDim.x) {
+      float4 v[4];
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int t = t0 + u * blockDim.x;
-        v[u] = (t < TCS_COARSE_TB * W && t / W < nb) ? rc[(size_t)b0 * W + t] : 0.f;
+        const int bb = t / TA4, a = 4 * (t - bb * TA4);
+        v[u] = (t < TCS_COARSE_TB * TA4 && bb < nb && a0 + a < ld)
+                   ? *(const float4*)(Einv + (size_t)(b0 + bb) * ld + a0 + a) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const int t = t0 + u * blockDim.x;
-        if (t < TCS_COARSE_TB * W) Rs[t] = v[u];
+        if (t < TCS_COARSE_TB * TA4) ((float4*)Es)[t] = v[u];
       }
     }
+    for (int t = threadIdx.x; t < TCS_COARSE_TB * W; t += blockDim.x) Rs[t] = (t / W < nb) ? rc[(size_t)b0 * W + t] : 0.f;
     __syncthreads();
-    if (local < rows_per) {
-#pragma unroll 8
-      for (int bb = 0; bb < TCS_COARSE_TB; ++bb) {
+    if (ks < KS) {
+      for (int bb = ks; bb < TCS_COARSE_TB; bb += KS) {
         const float4 e = *(const float4*)(Es + bb * TA + 4 * local);
         const float4 r = *(const float4*)(Rs + bb * W + 4 * q);
         acc[0].x += e.x * r.x; acc[0].y += e.x * r.y; acc[0].z += e.x * r.z; acc[0].w += e.x * r.w;
@@ -241,7 +237,7 @@ __global__ void __launch_bounds__(256) k_coarse_gemm(int m, int Q, int b_per_par
     }
     __syncthreads();
   }
-  if (local < rows_per) {
+  if (ks < KS) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int a = a0 + 4 * local + i;
@@ -294,8 +290,7 @@ static inline int env_i(const char* name, int dflt) { const char* v = getenv(nam
 // rc = Z^T R, y = E^-1 rc, rz += rc . y   (R at working width 4 Q)
 inline int apply(tcs_ctx* ctx, Level& Lv, int Q, const float4* R4, double* rz_target) {
   const int W = 4 * Q;
-  LAUNCH(ctx, k_restrict, Lv.nblk, 256, Lv.restrict_smem, Lv.n, Q, Lv.blk, R4, Lv.agg.p, Lv.first.p, Lv.rc.p);
-  CK(cudaMemsetAsync(Lv.y.p, 0, (size_t)Lv.m * W * sizeof(float), ctx->stream));
+  LAUNCH(ctx, k_restrict, Lv.nblk, 256, Lv.restrict_smem, Lv.n, Q, Lv.blk, R4, Lv.agg.p, Lv.first.p, Lv.rc.p, Lv.y.p);
   const int rows_per = std::min(256 / Q, 32);
   const int TA = 4 * rows_per;
   const unsigned gx = div_up(Lv.m, TA);
@@ -304,8 +299,10 @@ inline int apply(tcs_ctx* ctx, Level& Lv, int Q, const float4* R4, double* rz_ta
   b_per_part = (b_per_part + TCS_COARSE_TB - 1) / TCS_COARSE_TB * TCS_COARSE_TB;
   parts = div_up(Lv.m, b_per_part);
   const size_t smem = (size_t)TCS_COARSE_TB * (TA + W) * sizeof(float);
-  LAUNCH(ctx, k_coarse_gemm, dim3(gx, parts), rows_per * Q, smem, Lv.m, Q, b_per_part, Lv.Einv.p, Lv.rc.p, Lv.y.p);
-  LAUNCH(ctx, k_coarse_dot, 16, 256, (size_t)W * sizeof(double), Lv.m, Q, (const float4*)Lv.rc.p, (const float4*)Lv.y.p,
+  const int KS = std::max(1, 256 / (rows_per * Q));
+  LAUNCH(ctx, k_coarse_gemm, dim3(gx, parts), KS * rows_per * Q, smem, Lv.m, Lv.ld, Q, rows_per, b_per_part, Lv.Einv.p,
+         Lv.rc.p, Lv.y.p);
+  LAUNCH(ctx, k_coarse_dot, 48, 256, (size_t)W * sizeof(double), Lv.m, Q, (const float4*)Lv.rc.p, (const float4*)Lv.y.p,
          rz_target);
   return TCS_OK;
 }
@@ -390,7 +387,7 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Level& Lv) {
   CK(cudaMemsetAsync(E.p, 0, (size_t)m * m * 8, ctx->stream));
   CK(cudaMemsetAsync(dsum.p, 0, (size_t)m * 8, ctx->stream));
   LAUNCH(ctx, k_assemble_E, div_up(n, 256), 256, 0, n, (int)m, S.rowptr.p, S.col.p, S.val.p, S.diag.p, Lv.agg.p, E.p, dsum.p);
-  LAUNCH(ctx, k_regularise, div_up(m, 256), 256, 0, (int)m, E.p, dsum.p, env_double("TCS_COARSE_EPS", 1e-8));
+  LAUNCH(ctx, k_regularise, div_up(m, 256), 256, 0, (int)m, E.p, dsum.p, env_double("TCS_COARSE_EPS", 1e-6));
   // one cuSOLVER handle per device for the life of the process (creating one costs tens of milliseconds and device
   // memory); the mutex covers enqueue + synchronise, the handle's workspace is not shared between streams in flight
   static std::mutex mu;
@@ -419,8 +416,9 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Level& Lv) {
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     return TCS_OK;
   }
-  TRY(Lv.Einv.alloc(ctx, (size_t)m * m));
-  LAUNCH(ctx, k_einv_f32, div_up((size_t)m * m, 256), 256, 0, (int)m, E.p, Lv.Einv.p);
+  Lv.ld = ((int)m + 3) & ~3;
+  TRY(Lv.Einv.alloc(ctx, (size_t)m * Lv.ld));
+  LAUNCH(ctx, k_einv_f32, div_up((size_t)m * Lv.ld, 256), 256, 0, (int)m, Lv.ld, E.p, Lv.Einv.p);
   TRY(Lv.rc.alloc(ctx, (size_t)m * Kp0)); TRY(Lv.y.alloc(ctx, (size_t)m * Kp0));
   Lv.n = n; Lv.m = (int)m; Lv.blk = blk; Lv.nblk = nblk;
   Lv.on = true;
