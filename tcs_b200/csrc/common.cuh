@@ -124,6 +124,7 @@ struct tcs_system {
   DBuf<int> col;          // nnz_off (row indices)
   DBuf<float> val;        // nnz_off (-w)
   DBuf<float> diag;       // n (degree)
+  DBuf<float> gdiag;      // n: diagonal excess d_i - sum_j w_ij (what the difference-form SpMM kernels multiply p_i by)
   DBuf<float> B;          // n x Kp row-major
   DBuf<uint32_t> row_vertex;  // n
   DBuf<int> row_of;       // V (-1 for non-rows)

@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(256, 2)
           const int2 e = cv_s[a];
           const float w = __int_as_float(e.y);
           const float4 t = *(const float4*)(Pq + e.x);
-          y.x += w * t.x; y.y += w * t.y; y.z += w * t.z; y.w += w * t.w;
+          y.x += w * (t.x - p.x); y.y += w * (t.y - p.y); y.z += w * (t.z - p.z); y.w += w * (t.w - p.w);
         }
         AP[(size_t)(r0 + lr) * Q + q] = y;
         acc[0] += (double)p.x * (double)y.x; acc[1] += (double)p.y * (double)y.y;

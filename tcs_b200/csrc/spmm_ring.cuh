@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(kRingThreads, 1)
           const uint32_t off = off_s[k * G];
           const float w = w_s[k * G];
           const float4 v = *(const float4*)(Pq + (off << 4));
-          y.x += w * v.x; y.y += w * v.y; y.z += w * v.z; y.w += w * v.w;
+          y.x += w * (v.x - p.x); y.y += w * (v.y - p.y); y.z += w * (v.z - p.z); y.w += w * (v.w - p.w);
         }
         if (row < n) {
           AP[(size_t)row * Q + q] = y;

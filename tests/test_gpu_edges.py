@@ -312,9 +312,9 @@ dist.destroy_process_group()
 
 @pytest.fixture
 def coarse_env():
-    """Force the second preconditioner level (csrc/coarse.cuh) on small systems: per-kernel path, no size threshold."""
+    """Switches of the multilevel preconditioner (csrc/amg.cuh), restored after the test."""
     import os
-    keys = ("TCS_COARSE", "TCS_COARSE_MIN_ROWS", "TCS_COOP", "TCS_COARSE_BLOCK", "TCS_COARSE_THETA")
+    keys = ("TCS_AMG", "TCS_AMG_MIN_ROWS", "TCS_COOP", "TCS_AMG_PASSES", "TCS_AMG_OVER", "TCS_AMG_PROBE")
     saved = {k: os.environ.get(k) for k in keys}
 
     def set_(**kw):
@@ -329,21 +329,21 @@ def coarse_env():
 
 
 @pytest.mark.parametrize("name", ["test1", "test47", "test60"])
-@pytest.mark.parametrize("block", [256, 4096])
-def test_two_level_preconditioner_matches_oracle_on_reference_scenes(ctx, scenes, coarse_env, name, block):
-    """The coarse level changes how fast the tolerance is reached, not what is accepted: same residual bound, labels
-    equal to the oracle's float64 direct solve, and fewer iterations than Jacobi alone."""
+@pytest.mark.parametrize("passes", [2, 3])
+def test_multilevel_preconditioner_matches_oracle_on_reference_scenes(ctx, scenes, coarse_env, name, passes):
+    """The hierarchy changes how fast the tolerance is reached, not what is accepted: same residual bound, labels
+    equal to the oracle's float64 direct solve, and far fewer iterations than Jacobi alone."""
     sc = scenes[name]
     sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
     ctx.upload_cloud(sc["xyz"], sc["rgba"])
-    coarse_env(TCS_COARSE=0, TCS_COOP=0)
+    coarse_env(TCS_AMG=0, TCS_COOP=0)
     r0 = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
-    coarse_env(TCS_COARSE=1, TCS_COARSE_MIN_ROWS=1, TCS_COOP=0, TCS_COARSE_BLOCK=block)
+    coarse_env(TCS_AMG=1, TCS_AMG_PASSES=passes)
     r1 = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
     ref = orc.segment_cloud(sc["xyz"], sc["rgba"], 0.006, sx, sl, preset=0, mode=orc.MODE_PARITY, solver=orc.SOLVE_LDLT_F64)
     i0, i1 = r0["info"].as_dict(), r1["info"].as_dict()
     assert r1["status"] == capi.OK and i1["converged"] and max(i1["rel_residual"]) <= 1e-6
-    assert i1["iterations"] < i0["iterations"], (i0["iterations"], i1["iterations"])
+    assert i1["iterations"] < i0["iterations"] // 8, (i0["iterations"], i1["iterations"])
     V = r1["graph"].V
     assert int(np.count_nonzero(r1["vertex_colour"] != ref["vertex_colour"])) <= max(3, V // 2000)
     assert int(np.count_nonzero(r1["vertex_colour"] != r0["vertex_colour"])) <= max(3, V // 2000)
@@ -351,14 +351,14 @@ def test_two_level_preconditioner_matches_oracle_on_reference_scenes(ctx, scenes
     r1["graph"].close()
 
 
-def test_two_level_preconditioner_on_a_large_scene(ctx, coarse_env):
-    """1280 x 960 synthetic scene (above the default size threshold): default settings against Jacobi alone, and a
-    label-column shard with the coarse level on."""
+def test_multilevel_preconditioner_on_a_large_scene(ctx, coarse_env):
+    """1280 x 960 synthetic scene (ring SpMM): default settings against Jacobi alone, and a label-column shard with the
+    hierarchy on."""
     from tcs_b200 import synth
     xyz, rgba, label = synth.make_scene(1280, 960, 15, 7)
     sx, sl, _ = seeds_from_labels(xyz, label, 0, 10)
     ctx.upload_cloud(xyz, rgba)
-    coarse_env(TCS_COARSE=0)
+    coarse_env(TCS_AMG=0)
     r0 = ctx.segment_cloud(0.005, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST)
     coarse_env()
     r1 = ctx.segment_cloud(0.005, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST)
@@ -368,7 +368,7 @@ def test_two_level_preconditioner_on_a_large_scene(ctx, coarse_env):
     assert i0["rows"] >= 150000
     for i in (i0, i1, i2):
         assert i["converged"] and max(i["rel_residual"]) <= 1e-6
-    assert i1["iterations"] < i0["iterations"] // 2, (i0["iterations"], i1["iterations"])
+    assert i1["iterations"] < i0["iterations"] // 8, (i0["iterations"], i1["iterations"])
     V = r1["graph"].V
     assert int(np.count_nonzero(r1["vertex_colour"] != r0["vertex_colour"])) <= max(3, V // 2000)
     for r in (r0, r1, r2):
