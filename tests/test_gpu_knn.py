@@ -153,7 +153,7 @@ def test_random_walker_on_knn_graph(ctx, scenes):
         colours[v] = 1 + int(np.searchsorted(labels, sl[s]))
     K = len(labels)
     st, cg, _, info = g.random_walker(colours, K)
-    so, co, _, _ = o.random_walker(colours, K, solver=orc.SOLVE_LDLT_F64)
-    assert st == 0 and so == 0
+    assert st == 0
     assert max(info.as_dict()["rel_residual"]) <= 1e-6
-    assert np.count_nonzero(cg != co) <= max(3, o.V // 2000)
+    import label_gate
+    label_gate.check_labels_direct("test1 subsampled, 8-nearest-neighbour graph", cg, o, colours, K)

@@ -7,6 +7,7 @@ direct (LDL^T) solve except at near-ties.
 import numpy as np
 import pytest
 
+import label_gate
 import orc
 from tcs_b200 import capi
 from tcs_b200.seeds import seeds_from_labels
@@ -130,7 +131,7 @@ def test_components_and_seed_lookup(ctx, scenes, name):
 @pytest.mark.parametrize("preset", [capi.PRESET_CLASS, capi.PRESET_CLI])
 def test_segment_cloud_matches_oracle(ctx, scenes, name, preset):
     """Whole class path.  Potentials: float64 residual <= 1e-6 per column (reported by the solver, re-checked here
-    against the oracle's system); labels equal to the oracle's LDL^T labels except at near-ties."""
+    against the oracle's system); labels equal to the oracle's LDL^T labels except at near-ties (tests/label_gate.py)."""
     sc = scenes[name]
     sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
     ctx.upload_cloud(sc["xyz"], sc["rgba"])
@@ -142,20 +143,50 @@ def test_segment_cloud_matches_oracle(ctx, scenes, name, preset):
     ref = orc.segment_cloud(sc["xyz"], sc["rgba"], 0.006, sx, sl, preset=preset, mode=orc.MODE_PARITY,
                             solver=orc.SOLVE_LDLT_F64)
     assert ref["status"] == 0 and ref["K"] == info["ncolours"]
-    vg, vo = r["vertex_colour"], ref["vertex_colour"]
-    assert len(vg) == len(vo)
-    diff = np.nonzero(vg != vo)[0]
-    if len(diff):
-        # every disagreement must be a documented near-tie: top-2 potential gap below 1e-4 in the oracle's potentials
-        g = r["graph"]
-        pot = np.zeros((info["ncolours"], g.V), np.float32)
-        capi.lib().tcs_graph_download_potentials(g.h, pot.ctypes.data)
-        top2 = np.sort(pot[:, diff], axis=0)[-2:]
-        assert np.all(top2[1] - top2[0] < 1e-4), (len(diff), (top2[1] - top2[0]).max())
-    assert len(diff) <= max(3, len(vg) // 2000)
+    # labels: every disagreement must be a near-tie of the ORACLE's float64 potentials (gap < 1e-6) and is recorded
+    ndiff = label_gate.check_labels("%s preset %s PARITY" % (name, "class" if preset == capi.PRESET_CLASS else "cli"),
+                                    r["vertex_colour"], ref, sx, sl, info=info)
     # point -> cluster map
     pg, po = r["point_cluster"], ref["point_cluster"]
-    assert np.count_nonzero(pg != po) <= 10 * max(1, len(diff))
+    assert np.count_nonzero(pg != po) <= 10 * ndiff
+
+
+def _c4_crop():
+    """The 1024 x 768 centre crop of the C4 scene that bench.py's CPU arm times."""
+    from tcs_b200 import synth
+    w, h, cw, ch = 4480, 2880, 1024, 768
+    xyz, rgba, label = synth.make_scene(w, h, 15, 20261104)
+    r0, c0 = (h - ch) // 2, (w - cw) // 2
+    cut = lambda a, *t: a.reshape(h, w, *t)[r0:r0 + ch, c0:c0 + cw].reshape(-1, *t).copy()
+    return cut(xyz, 3), cut(rgba), cut(label)
+
+
+@pytest.mark.parametrize("case", ["c5-0", "c5-1", "c5-2", "c4-crop"])
+def test_fast_mode_default_solver_matches_oracle(ctx, case):
+    """The BENCHMARKED configuration - FAST arithmetic mode, default solver path (multilevel-preconditioned PCG, tiled /
+    ring SpMM) - against the oracle's FAST-mode pipeline with the float64 direct solve: three C5 scenes and the
+    C4 centre crop bench.py's CPU arm runs."""
+    from tcs_b200 import synth
+    if case == "c4-crop":
+        xyz, rgba, label = _c4_crop()
+        res, per, sid = 0.005, 10, 0
+    else:
+        sid = int(case[3:])
+        xyz, rgba, label = synth.make_c5(sid)
+        res, per = 0.006, 5
+    sx, sl, _ = seeds_from_labels(xyz, label, sid, per)
+    ctx.upload_cloud(xyz, rgba)
+    r = ctx.segment_cloud(res, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST)
+    info = r["info"].as_dict()
+    assert r["status"] == capi.OK and info["converged"] and max(info["rel_residual"]) <= 1e-6
+    ref = orc.segment_cloud(xyz, rgba, res, sx, sl, preset=0, mode=orc.MODE_FAST, solver=orc.SOLVE_LDLT_F64)
+    g, o = r["graph"], ref["graph"]
+    assert (g.V, g.E) == (o.V, o.E)
+    for a, b in zip(g.csr(), o.csr()):
+        assert np.array_equal(a, b)
+    ndiff = label_gate.check_labels("%s FAST" % case, r["vertex_colour"], ref, sx, sl, info=info)
+    assert np.count_nonzero(r["point_cluster"] != ref["point_cluster"]) <= 10 * ndiff
+    g.close()
 
 
 def test_potentials_match_direct_solve(ctx, scenes):
@@ -259,3 +290,59 @@ def test_column_compaction_is_transparent(ctx, shape, monkeypatch):
         assert np.count_nonzero(out[name][0] != out["keep"][0]) <= max(3, len(out[name][0]) // 1000), name
         assert np.all(np.abs(out[name][1].sum(axis=0) - out["keep"][1].sum(axis=0)) < 5e-2)
         assert out[name][2] <= out["keep"][2] + 50
+
+
+@pytest.mark.parametrize("name", ["test1", "test56"])
+@pytest.mark.parametrize("policy", ["ignore", "remove"])
+def test_small_weight_policies_match_oracle(ctx, scenes, name, policy):
+    """SMALL_WEIGHT_IGNORE and SMALL_WEIGHT_REMOVE_EDGE (graph/impl/edge_weight_computer.hpp:163-187): weights bit-exact,
+    and for REMOVE_EDGE the compacted edge list and out-edge lists equal the oracle's (remove_edge_if keeps the relative
+    order); the random walker then runs on the pruned graph.  Threshold 0.05 removes ~10 % of the edges."""
+    sc = scenes[name]
+    g, o = _build_both(ctx, sc, 0.006)
+    pol_g = capi.SMALL_IGNORE if policy == "ignore" else capi.SMALL_REMOVE
+    pol_o = orc.SMALL_IGNORE if policy == "ignore" else orc.SMALL_REMOVE
+    for h, mode in ((g, capi.MODE_PARITY), (o, orc.MODE_PARITY)):
+        h.normals(mode=mode)
+        h.signed_curvatures()
+    E0 = o.E
+    g.edge_weights(capi.TERMS_CLASS, threshold=0.05, policy=pol_g, mode=capi.MODE_PARITY)
+    o.edge_weights(orc.PRESET_CLASS, threshold=0.05, policy=pol_o, mode=orc.MODE_PARITY)
+    assert (g.V, g.E) == (o.V, o.E)
+    if policy == "remove":
+        assert 0.5 * E0 < o.E < 0.98 * E0, (E0, o.E)
+    else:
+        assert o.E == E0 and (o.edges()[2] < 0.05).any()      # small weights stay as they are
+    for a, b in zip(g.edges()[:2], o.edges()[:2]):
+        assert np.array_equal(a, b)
+    assert np.array_equal(_bits(g.edges()[2]), _bits(o.edges()[2]))
+    for a, b in zip(g.csr(), o.csr()):
+        assert np.array_equal(a, b)
+    nc_g, comp_g = g.components()
+    nc_o, comp_o = o.components()
+    assert nc_g == nc_o and np.array_equal(comp_g, comp_o)
+    sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
+    colours, K = label_gate.seed_colours(o, sx, sl)
+    st, cg, _, info = g.random_walker(colours, K)
+    assert st == 0 and max(info.as_dict()["rel_residual"]) <= 1e-6
+    label_gate.check_labels_direct("%s small-weight policy %s (threshold 0.05) PARITY" % (name, policy), cg, o, colours, K)
+    g.close()
+
+
+@pytest.mark.parametrize("name", ["test13", "test60"])
+def test_one_ring_normals_bit_exact(ctx, scenes, name):
+    """computeNormalsAndCurvatures(g, neighborhood_1ring = true) (graph/impl/common.hpp:64-76): the 1-ring multiset."""
+    g, o = _build_both(ctx, scenes[name], 0.006)
+    g.normals(one_ring=True, mode=capi.MODE_PARITY)
+    o.normals(one_ring=True, mode=orc.MODE_PARITY)
+    _, _, gn, gc = g.vertices()
+    _, _, on, oc = o.vertices()
+    assert np.count_nonzero(_bits(gn) != _bits(on)) == 0 and np.count_nonzero(_bits(gc) != _bits(oc)) == 0
+    # and it is a different result from the default 2-ring neighbourhood
+    g.normals(one_ring=False, mode=capi.MODE_PARITY)
+    assert np.count_nonzero(_bits(g.vertices()[2]) != _bits(on)) > 0
+    # FAST mode, 1-ring, against the oracle's FAST definition
+    g.normals(one_ring=True, mode=capi.MODE_FAST)
+    o.normals(one_ring=True, mode=orc.MODE_FAST)
+    assert np.count_nonzero(_bits(g.vertices()[2]) != _bits(o.vertices()[2])) <= 4 * 8
+    g.close()

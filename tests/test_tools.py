@@ -108,7 +108,8 @@ def test_app_refuses_to_run_without_seeds_or_gpu(tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name,res", [("test1", 0.006), ("test1", 0.01), ("test47", 0.006)])
+@pytest.mark.parametrize("name,res", [("test1", 0.006), ("test1", 0.01), ("test13", 0.006), ("test47", 0.006),
+                                      ("test56", 0.006), ("test60", 0.006)])
 def test_app_matches_oracle_and_scores(scenes, tmp_path, name, res):
     """BASELINE configs 1-3: <scene>.pcd [-v R] --load-seeds seeds.pcd --save, then the evaluation tool on the result."""
     import orc
@@ -130,8 +131,13 @@ def test_app_matches_oracle_and_scores(scenes, tmp_path, name, res):
     ref = orc.segment_cloud(xyz, rgba, res, sx, sl, preset=1, solver=orc.SOLVE_LDLT_F64)   # the CLI pipeline
     p2v = ref["graph"].point_to_vertex()
     want = np.where(p2v == 0xFFFFFFFF, 0, ref["vertex_colour"][np.minimum(p2v, ref["graph"].V - 1)])
-    bad = int(np.count_nonzero(got["label"] != want))
-    assert bad <= 10 * max(3, ref["graph"].V // 2000), bad
+    # per-point labels: a point may differ only where its vertex is a near-tie of the oracle's potentials
+    import label_gate
+    wrong = np.nonzero(got["label"] != want)[0]
+    assert np.all(p2v[wrong] != 0xFFFFFFFF)
+    vcol = ref["vertex_colour"].copy()
+    vcol[p2v[wrong]] = got["label"][wrong]
+    label_gate.check_labels("%s @%g app (cli preset)" % (name, res), vcol, ref, sx, sl)
     # the evaluation tool on the saved file agrees with the rule evaluated in Python
     r = subprocess.run([EVAL, out, cloud], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
