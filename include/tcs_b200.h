@@ -175,6 +175,25 @@ int tcs_random_walker(tcs_graph* g, uint32_t* colours, int ncolours, const tcs_s
 int tcs_segment_cloud(tcs_ctx* ctx, float resolution, int preset, int mode, const float* seed_xyz,
                       const uint32_t* seed_label, size_t ns, const tcs_solver_opts* opts, int32_t* point_cluster,
                       uint32_t* vertex_colour, tcs_solve_info* info, tcs_graph** out);
+/* Batched class path (BASELINE configs[4]): `nscenes` independent clouds, one segment() each in
+ * the reference (impl/random_walker_segmentation.hpp:138-224).  Graphs, features and weights are computed scene by
+ * scene; the random-walker systems of all scenes are solved together as ONE block-diagonal system (scenes are
+ * independent: label column k of the batch is the union of the scenes' k-th columns), with the float64 convergence
+ * test applied per scene and column.  Results per scene equal those of tcs_segment_cloud on that scene up to the
+ * solver tolerance.  info (may be NULL) describes the joint solve. */
+typedef struct tcs_scene {
+  const float* xyz; size_t xyz_stride;         /* in: as tcs_cloud_upload */
+  const uint32_t* rgba; size_t rgba_stride;    /* in: NULL for uncoloured clouds */
+  size_t n;
+  const float* seed_xyz; const uint32_t* seed_label; size_t ns;   /* in: setSeeds */
+  int32_t* point_cluster;                      /* out: n int32 (may be NULL) */
+  uint32_t* vertex_colour;                     /* out: capacity n >= V uint32 (may be NULL) */
+  size_t V, E;                                 /* out */
+  int ncolours;                                /* out: K of this scene */
+  int status;                                  /* out */
+} tcs_scene;
+int tcs_segment_batch(tcs_ctx* ctx, tcs_scene* scenes, int nscenes, float resolution, int preset, int mode,
+                      const tcs_solver_opts* opts, tcs_solve_info* info);
 /* potentials kept by store_potentials (getPotentials, random_walker_segmentation.h:251): V x K column-major */
 int tcs_graph_download_potentials(tcs_graph* g, float* potentials);
 int tcs_graph_download_colours(tcs_graph* g, uint32_t* colours);

@@ -38,7 +38,7 @@ EXPORTS = [
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
     "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm", "tcs_graph_download_best",
-    "tcs_build_nn_graph",
+    "tcs_build_nn_graph", "tcs_segment_batch",
 ]
 
 
@@ -64,6 +64,14 @@ class SolveInfo(C.Structure):
                     rel_residual=[self.rel_residual[k] for k in range(K)], spmm_ms=self.spmm_ms,
                     spmm_launches=self.spmm_launches, solve_ms=self.solve_ms, stage_ms=list(self.stage_ms),
                     spmm_kernel=self.spmm_kernel)
+
+
+class Scene(C.Structure):
+    """tcs_scene: one cloud + seeds of a batch (tcs_segment_batch)."""
+    _fields_ = [("xyz", C.c_void_p), ("xyz_stride", C.c_size_t), ("rgba", C.c_void_p), ("rgba_stride", C.c_size_t),
+                ("n", C.c_size_t), ("seed_xyz", C.c_void_p), ("seed_label", C.c_void_p), ("ns", C.c_size_t),
+                ("point_cluster", C.c_void_p), ("vertex_colour", C.c_void_p), ("V", C.c_size_t), ("E", C.c_size_t),
+                ("ncolours", C.c_int), ("status", C.c_int)]
 
 
 class TcsError(RuntimeError):
@@ -124,6 +132,7 @@ def lib():
     L.tcs_nearest_vertices.argtypes = [vp, vp, sz, vp]
     L.tcs_random_walker.argtypes = [vp, vp, ci, C.POINTER(SolverOpts), vp, C.POINTER(SolveInfo)]
     L.tcs_segment_cloud.argtypes = [vp, cf, ci, ci, vp, vp, sz, C.POINTER(SolverOpts), vp, vp, C.POINTER(SolveInfo), PP]
+    L.tcs_segment_batch.argtypes = [vp, C.POINTER(Scene), ci, cf, ci, ci, C.POINTER(SolverOpts), C.POINTER(SolveInfo)]
     L.tcs_graph_download_potentials.argtypes = [vp, vp]
     L.tcs_graph_download_colours.argtypes = [vp, vp]
     L.tcs_graph_d_colours.argtypes = [vp]
@@ -250,6 +259,28 @@ class Context:
         g = Graph(self, h)
         return dict(graph=g, point_cluster=pc, vertex_colour=None if vc is None else vc[:g.V].copy(), info=info,
                     status=st)
+
+    def segment_batch(self, scenes, resolution, preset=PRESET_CLASS, mode=MODE_PARITY, opts=None):
+        """Batched class path (tcs_segment_batch).  scenes: list of (xyz (n,3) f32, rgba (n,) u32 or None, seed_xyz,
+        seed_label).  Returns (list of dict(point_cluster, vertex_colour, V, E, K), SolveInfo of the joint solve, status)."""
+        arr = (Scene * len(scenes))()
+        keep = []
+        for i, (xyz, rgba, sx, sl) in enumerate(scenes):
+            xyz, rgba, sx, sl = _f32(xyz), _u32(rgba), _f32(sx), _u32(sl)
+            pc, vc = np.zeros(len(xyz), np.int32), np.zeros(len(xyz), np.uint32)
+            keep.append((xyz, rgba, sx, sl, pc, vc))
+            a = arr[i]
+            a.xyz, a.xyz_stride, a.n = xyz.ctypes.data, 12, len(xyz)
+            a.rgba, a.rgba_stride = (rgba.ctypes.data if rgba is not None else None), 4
+            a.seed_xyz, a.seed_label, a.ns = sx.ctypes.data, sl.ctypes.data, len(sl)
+            a.point_cluster, a.vertex_colour = pc.ctypes.data, vc.ctypes.data
+        opts = opts or default_opts()
+        info = SolveInfo()
+        st = self.check(lib().tcs_segment_batch(self.h, arr, len(scenes), resolution, preset, mode, C.byref(opts),
+                                                C.byref(info)), allow=(ERR_NOT_CONVERGED,))
+        out = [dict(point_cluster=k[4], vertex_colour=k[5][:arr[i].V].copy(), V=arr[i].V, E=arr[i].E, K=arr[i].ncolours)
+               for i, k in enumerate(keep)]
+        return out, info, st
 
     n_points_hint = 0
 

@@ -195,6 +195,17 @@ int tcs_impl_sort_pairs_u32(tcs_ctx* ctx, uint32_t* key_in, uint32_t* key_out, u
 int tcs_impl_sort_pairs_u64(tcs_ctx* ctx, uint64_t* key_in, uint64_t* key_out, uint32_t* val_in, uint32_t* val_out,
                             size_t n, int end_bit);
 
+// block-diagonal system of several scenes: rows [row_begin[s], row_begin[s + 1]) belong to scene s
+struct tcs_segments {
+  std::vector<int> row_begin;
+  int count() const { return row_begin.empty() ? 0 : (int)row_begin.size() - 1; }
+};
+struct tcs_pcg_result {
+  int iterations = 0, converged = 1, kernel = 0, spmm_launches = 0;
+  float spmm_ms = 0.f;
+  double rel[TCS_MAX_LABELS] = {0};
+};
+
 // solve.cu / pcg.cu
 int tcs_impl_components(tcs_graph* g);
 int tcs_impl_nearest_vertices(tcs_graph* g, const float* seed_xyz, size_t ns, DBuf<int32_t>& d_nearest);
@@ -203,3 +214,7 @@ int tcs_impl_assemble(tcs_graph* g, int K);
 // PCG + argmax on g->colours (device, seeds in / labels out); fills info (may be NULL)
 int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts, tcs_solve_info* info);
 int tcs_impl_point_clusters(tcs_graph* g, int K);
+int tcs_impl_pcg_solve(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts& opts, const tcs_segments* seg,
+                       tcs_pcg_result& res);
+int tcs_impl_argmax(tcs_graph* g, const uint32_t* row_vertex, int nrows, int K, int Kp, const double* X,
+                    const tcs_solver_opts& opts, float* d_pot, tcs_solve_info* info);

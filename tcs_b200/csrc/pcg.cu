@@ -238,6 +238,21 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
   }
 }
 
+// out[c] = sum over rows [row0, row0 + n) of B[row][c]^2 (float64): ||b||^2 of one scene of a block-diagonal batch
+__global__ void __launch_bounds__(256) k_col_sumsq(int row0, int n, int Q, const float4* __restrict__ B, double* __restrict__ out) {
+  extern __shared__ double sm[];
+  const int rows_per_block = blockDim.x / Q;
+  const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
+  const bool active = local < rows_per_block;
+  double acc[4] = {0, 0, 0, 0};
+  if (active)
+    for (int lrow = blockIdx.x * rows_per_block + local; lrow < n; lrow += gridDim.x * rows_per_block) {
+      const float4 b = B[(size_t)(row0 + lrow) * Q + q];
+      acc[0] += (double)b.x * b.x; acc[1] += (double)b.y * b.y; acc[2] += (double)b.z * b.z; acc[3] += (double)b.w * b.w;
+    }
+  reduce_columns(acc, q, Q, active, sm, out, true);
+}
+
 // X += xd ; xd = 0  (before every float64 true residual)
 __global__ void k_flush_x(size_t count, double* __restrict__ X, float* __restrict__ Xd) {
   const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -369,7 +384,8 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
 // and the float32 x increments accumulated), so the step after a replacement uses the exact line search
 // alpha = p.r / p.Ap instead of r.z / p.Ap: with r.z the step overshoots by (|r_true| / |r_recurrence|)^2 and a
 // column that is almost converged diverges.
-__global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint32_t* __restrict__ rowptr,
+// Rows [row0, row0 + n) of the system (one scene of a block-diagonal batch, or all rows).
+__global__ void __launch_bounds__(256) k_true_residual(int row0, int n, int Q, const uint32_t* __restrict__ rowptr,
                                                        const int* __restrict__ col, const float* __restrict__ val,
                                                        const float* __restrict__ diag, const float4* __restrict__ B,
                                                        const double* __restrict__ X, const float4* __restrict__ P,
@@ -381,7 +397,8 @@ __global__ void __launch_bounds__(256) k_true_residual(int n, int Q, const uint3
   const bool active = local < rows_per_block;
   double a_rr[4] = {0, 0, 0, 0}, a_rz[4] = {0, 0, 0, 0}, a_pr[4] = {0, 0, 0, 0};
   if (active) {
-    for (int row = blockIdx.x * rows_per_block + local; row < n; row += gridDim.x * rows_per_block) {
+    for (int lrow = blockIdx.x * rows_per_block + local; lrow < n; lrow += gridDim.x * rows_per_block) {
+      const int row = row0 + lrow;
       const size_t i = (size_t)row * Q + q;
       const double d = (double)diag[row];
       const double2* xp = (const double2*)(X + 4 * i);
@@ -1030,6 +1047,494 @@ PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q) {
 
 }  // namespace
 
+#include "pcg_batch.cuh"
+
+// Multi-right-hand-side PCG on an assembled system S (S.B in, S.X out as n x S.Kp float64).  `seg` (may be NULL)
+// describes a block-diagonal system of several scenes: the float64 convergence test is then applied per scene and
+// column (a column is done when EVERY scene's relative residual has reached the tolerance).
+int tcs_impl_pcg_solve(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts& opts, const tcs_segments* seg,
+                       tcs_pcg_result& res) {
+  const int n = S.n, Kp = S.Kp, Q = Kp / 4;
+  res = tcs_pcg_result();
+  if (n <= 0 || K <= 0) return TCS_OK;
+  TRY(S.gdiag.alloc(ctx, (size_t)n + 8));
+  LAUNCH(ctx, k_diag_excess, div_up(n, 256), 256, 0, n, S.rowptr.p, S.val.p, S.diag.p, S.gdiag.p);
+  if (seg && seg->count() > 1 && env_int("TCS_BATCH_PCG", 1) != 0) {
+    // a batch of independent scenes: every (scene, column) pair runs its own recurrence (pcg_batch.cuh)
+    bool ran = false;
+    TRY(pcg_solve_batched(ctx, S, K, opts, *seg, res, &ran));
+    if (ran) return TCS_OK;
+  }
+  int iterations = 0, converged = 1, kernel_at_start = 0;
+  double rel[TCS_MAX_LABELS] = {0};
+  float spmm_sum_ms = 0.f;
+  int spmm_timed = 0, spmm_launches = 0;
+
+  // Working set: the label columns still iterating, packed to a multiple of 4.  wmap[kw] = original column of working
+  // column kw (-1 = padding).  Columns are independent systems (one right-hand side each): when enough of them
+  // have reached the tolerance to drop a float4 of columns, the survivors are re-packed and the SpMM re-planned
+  // for the narrower rows, so converged columns stop costing bandwidth (C4: 6 of 16 columns finish within 700 of
+  // 8050 iterations).  TCS_COMPACT=0 keeps all columns (they are then frozen instead).
+  const int Kp0 = Kp;
+  int Kw = Kp0, Qw = Q;
+  std::vector<int> wmap(Kw);
+  for (int k = 0; k < Kw; ++k) wmap[k] = k < K ? k : -1;
+  std::vector<char> done(K, 0);
+  bool compact_enabled = env_int("TCS_COMPACT", 1) != 0 && !(seg && seg->count() > 1);
+  bool compacted = false;
+  bool dropped_columns = false;  // converged columns have left the working set (SpMM timing samples stop there)
+  const size_t nk = (size_t)n * Kp0;
+  DBuf<double> Xw;   // float64 solution of the working columns (becomes S.X when no compaction happens)
+  DBuf<float> Xd;    // float32 increment since the last flush
+  DBuf<float> Bw;    // right-hand sides of the working columns (S.B itself until the first compaction)
+  S.X.release();
+  TRY(Xw.alloc(ctx, nk)); TRY(Xd.alloc(ctx, nk));
+  TRY(S.P.alloc(ctx, nk)); TRY(S.R.alloc(ctx, nk)); TRY(S.AP.alloc(ctx, nk));
+  DBuf<float> invd;
+  TRY(invd.alloc(ctx, n));
+  // scalar accumulators, row stride Kp0: pAp[3], rz[3], rr, bb, rz of the initial residual, p.r, recurrence rr[3]
+  const int kScalRows = 13;
+  DBuf<double> scal;
+  TRY(scal.alloc(ctx, (size_t)kScalRows * Kp0));
+  CK(cudaMemsetAsync(scal.p, 0, (size_t)kScalRows * Kp0 * 8, ctx->stream));
+  double* d_pAp = scal.p;
+  double* d_rz = scal.p + 3 * Kp0;
+  double* d_rr = scal.p + 6 * Kp0;
+  double* d_bb = scal.p + 7 * Kp0;
+  double* d_rz0 = scal.p + 8 * Kp0;
+  double* d_pr = scal.p + 9 * Kp0;   // p . r of the last residual replacement
+  double* d_rr3 = scal.p + 10 * Kp0; // ||r||^2 of the recurrence residual (three generations, like rz)
+  // block-diagonal batch: per-scene ||r||^2 and ||b||^2 (scene-major, stride Kp0), agg / worst ratio per column
+  const int nseg = (seg && seg->count() > 1) ? seg->count() : 0;
+  DBuf<double> seg_rr;
+  std::vector<double> h_seg_rr, h_seg_bb, seg_scale((size_t)Kp0, 1.0);
+  if (nseg) {
+    TRY(seg_rr.alloc(ctx, 2 * (size_t)nseg * Kp0));
+    CK(cudaMemsetAsync(seg_rr.p, 0, 2 * (size_t)nseg * Kp0 * 8, ctx->stream));
+    h_seg_rr.resize((size_t)nseg * Kp0);
+    h_seg_bb.resize((size_t)nseg * Kp0);
+  }
+  // device-side "done": recurrence residual four decades below the tolerance (in the D^-1 norm, relative to b) -
+  // far from the tolerance itself (the two norms differ), far above float32 underflow of r
+  const double done_factor = 1e-8 * opts.tolerance * opts.tolerance;
+  DBuf<int> frozen, d_cols;
+  TRY(frozen.alloc(ctx, Kp0)); TRY(d_cols.alloc(ctx, 2 * (size_t)Kp0));
+  CK(cudaMemsetAsync(frozen.p, 0, (size_t)Kp0 * 4, ctx->stream));
+  int* h_frozen = (int*)((char*)ctx->h_pin + 2048);
+  for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
+  PcgLaunch L = pcg_launch_shape(ctx, n, Qw);
+  // small systems: whole chunks of iterations in one persistent cooperative launch (k_pcg_chunk) instead of three
+  // launches per iteration; no SpMM plan is needed then (the measurement hooks plan on demand)
+  DBuf<unsigned> coop_bar;
+  DBuf<double> coop_part;     // per-CTA partial dot products
+  DBuf<long long> coop_dbg;   // TCS_DEBUG: cycles per phase of the first and the last CTA
+  TRY(coop_bar.alloc(ctx, 1));
+  if (getenv("TCS_DEBUG")) TRY(coop_dbg.alloc(ctx, 16));
+  unsigned coop_grid = 0;
+  bool coop_disabled = false;
+  int coop_M = 0, coop_cap = 0;
+  size_t coop_smem = 0;
+  const void* coop_fn = nullptr;
+  auto plan_iteration = [&]() -> int {
+    coop_grid = 0;
+    const int rows_per_block = 256 / Qw;
+    const int ntiles = (n + rows_per_block - 1) / rows_per_block;
+    // at most 4 row tiles per CTA, all CTAs co-resident: n * Q <= ~1.2 M (a 640 x 480 scene with 16 labels is 0.2 M)
+    if (!coop_disabled && env_int("TCS_COOP", 1) != 0 && !opts.time_spmm && !getenv("TCS_SPMM") && ntiles <= 4 * 8 * ctx->sm_count &&
+        n <= env_int("TCS_COOP_MAX_ROWS", 100000)) {
+      uint32_t* d_max = (uint32_t*)ctx->d_scal + 16;
+      CK(cudaMemsetAsync(d_max, 0, 4, ctx->stream));
+      LAUNCH(ctx, k_tile_max_nnz, div_up(ntiles, 256), 256, 0, n, rows_per_block, S.rowptr.p, d_max);
+      uint32_t mx = 0;
+      TRY(tcs_impl_read_u32(ctx, d_max, &mx));
+      const int cap = (int)((mx + 1u) & ~1u);
+      const void* fns[4] = {(const void*)k_pcg_chunk<1>, (const void*)k_pcg_chunk<2>, (const void*)k_pcg_chunk<3>,
+                            (const void*)k_pcg_chunk<4>};
+      const int max_ctas = env_int("TCS_COOP_CTAS", 8);
+      for (int M = 1; M <= 4; ++M) {
+        const size_t smem = (size_t)M * cap * 8 + 256 * 4 * 8 + (size_t)Kw * (4 * 8 + 3 * 4);
+        if (smem > 200 * 1024) break;
+        // always the same value: function attributes are shared by every host thread that drives this device
+        if (cudaFuncSetAttribute(fns[M - 1], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) {
+          cudaGetLastError();
+          break;
+        }
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fns[M - 1], 256, smem) != cudaSuccess || nb < 1) { cudaGetLastError(); break; }
+        const int resident = ctx->sm_count * std::min(nb, max_ctas);
+        const int grid = (ntiles + M - 1) / M;
+        if (grid > resident) continue;
+        coop_grid = (unsigned)grid; coop_M = M; coop_cap = cap; coop_smem = smem; coop_fn = fns[M - 1];
+        if (getenv("TCS_DEBUG"))
+          fprintf(stderr, "[tcs] chunk plan: n=%d Q=%d tiles=%d cap=%d M=%d grid=%d smem=%zu occupancy=%d\n", n, Qw, ntiles, cap, M, grid, smem, nb);
+        TRY(coop_part.alloc(ctx, 2 * (size_t)grid * Kw));
+        S.ring = S.tiled = false;
+        S.plan_stale = true;
+        return TCS_OK;
+      }
+    }
+    return spmm_plan(ctx, S);
+  };
+  {
+    const unsigned sleep_ns = (unsigned)env_int("TCS_COOP_SLEEP", 0);
+    CK(cudaMemcpyToSymbolAsync(c_coop_sleep, &sleep_ns, 4, 0, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  // coarse levels of the preconditioner (amg.cuh); with them the solve runs on the per-kernel path
+  amg::Hierarchy AH;
+  TRY(amg::setup(ctx, S, Kp0, AH));
+  if (AH.on) {
+    coop_disabled = true;
+    // a few dozen iterations in all: re-planning the SpMM for a narrower working set costs more than it saves
+    if (!getenv("TCS_COMPACT")) compact_enabled = false;
+  }
+  TRY(plan_iteration());
+  kernel_at_start = coop_grid ? 4 : S.ring ? 3 : S.tiled ? 2 : 1;
+  const float4* B4 = (const float4*)S.B.p;
+  float4* P4 = (float4*)S.P.p;
+  float4* R4 = (float4*)S.R.p;
+  float4* AP4 = (float4*)S.AP.p;
+  LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Qw, B4, S.diag.p, invd.p, R4, P4, Xw.p, (float4*)Xd.p, d_rz, d_bb);
+  if (AH.on) {
+    TRY(amg::apply(ctx, AH, Qw, R4, d_rz));
+    LAUNCH(ctx, amg::k_prolong, div_up((size_t)n * Qw, 256), 256, 0, n, Qw, 1.0f, amg::fine_agg(AH), amg::result(AH), P4);
+  }
+  CK(cudaMemcpyAsync(d_rz0, d_rz, (size_t)Kp0 * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+  if (nseg) {
+    double* d_bb_seg = seg_rr.p + (size_t)nseg * Kp0;
+    for (int sg = 0; sg < nseg; ++sg) {
+      const int r0 = seg->row_begin[sg], nr = seg->row_begin[sg + 1] - r0;
+      if (nr > 0)
+        LAUNCH(ctx, k_col_sumsq, std::min(L.grid, div_up(nr, 256 / Qw)), L.block, L.smem, r0, nr, Qw, B4, d_bb_seg + (size_t)sg * Kp0);
+    }
+    CK(cudaMemcpyAsync(h_seg_bb.data(), d_bb_seg, (size_t)nseg * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  std::vector<double> h((size_t)kScalRows * Kp0);
+  // sampled SpMM timing: one event pair per launch for the first launches (full width)
+  const int kMaxSamples = 64;
+  std::vector<cudaEvent_t> evs;
+  if (opts.time_spmm) {
+    evs.resize(2 * kMaxSamples);
+    for (auto& e : evs) CK(cudaEventCreate(&e));
+  }
+  int samples = 0;
+  converged = 0;
+  int it = 0;
+  // TCS_DEBUG: wall-clock per phase (we synchronise at every check, so host time brackets device time)
+  auto phase_t0 = std::chrono::steady_clock::now();
+  int phase_it0 = 0;
+  auto phase_report = [&](const char* what) {
+    if (!getenv("TCS_DEBUG")) return;
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - phase_t0).count();
+    fprintf(stderr, "[tcs] %s: iterations %d..%d at width %d, kernel %d: %.1f ms = %.1f us / iteration\n", what, phase_it0, it,
+            Kw, S.ring ? 3 : S.tiled ? 2 : 1, ms, it > phase_it0 ? 1e3 * ms / (it - phase_it0) : 0.0);
+    phase_t0 = std::chrono::steady_clock::now();
+    phase_it0 = it;
+  };
+  // ---- re-pack the working set to the columns that are not done (newKw = their count rounded up to 4)
+  auto compact = [&](int newKw, int active_cols) -> int {
+    const size_t nkw = (size_t)n * Kw;
+    // ---- drop the converged columns
+    phase_report("compaction");
+    if (!S.X.p) {
+      TRY(S.X.alloc(ctx, nk));
+      CK(cudaMemsetAsync(S.X.p, 0, nk * 8, ctx->stream));
+    }
+    std::vector<int> cols(2 * (size_t)Kp0, -1), newmap;  // [0, Kp0): scatter targets; [Kp0, 2 Kp0): repack sources
+    for (int kw = 0; kw < Kw; ++kw) {
+      cols[kw] = wmap[kw];
+      if (wmap[kw] >= 0 && !done[wmap[kw]]) { cols[Kp0 + newmap.size()] = kw; newmap.push_back(wmap[kw]); }
+    }
+    newmap.resize(newKw, -1);
+    CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+    LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
+    const size_t nk2 = (size_t)n * newKw;
+    DBuf<float> P2, R2, B2, Xd2, AP2;
+    DBuf<double> X2;
+    TRY(P2.alloc(ctx, nk2)); TRY(R2.alloc(ctx, nk2)); TRY(B2.alloc(ctx, nk2)); TRY(Xd2.alloc(ctx, nk2));
+    TRY(AP2.alloc(ctx, nk2)); TRY(X2.alloc(ctx, nk2));
+    const int* src = d_cols.p + Kp0;
+    LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.P.p, P2.p);
+    LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.R.p, R2.p);
+    LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src,
+           Bw.p ? Bw.p : S.B.p, B2.p);
+    LAUNCH(ctx, k_repack_columns<double>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, Xw.p, X2.p);
+    CK(cudaMemsetAsync(Xd2.p, 0, nk2 * 4, ctx->stream));
+    // per-column scalars: same permutation on the host (we are at a synchronisation point anyway)
+    CK(cudaMemcpyAsync(h.data(), scal.p, (size_t)kScalRows * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));  // also: `cols` was read by the copy above
+    std::vector<double> h2((size_t)kScalRows * Kp0, 0.0);
+    for (int r8 = 0; r8 < kScalRows; ++r8)
+      for (int k2 = 0; k2 < newKw; ++k2)
+        if (cols[Kp0 + k2] >= 0) h2[(size_t)r8 * Kp0 + k2] = h[(size_t)r8 * Kp0 + cols[Kp0 + k2]];
+    CK(cudaMemcpyAsync(scal.p, h2.data(), (size_t)kScalRows * Kp0 * 8, cudaMemcpyHostToDevice, ctx->stream));
+    for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
+    CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));  // h2 is a local vector
+    S.P.swap(P2); S.R.swap(R2); S.AP.swap(AP2); Bw.swap(B2); Xw.swap(X2); Xd.swap(Xd2);
+    Kw = newKw; Qw = Kw / 4; wmap = newmap;
+    S.Kp = Kw;
+    compacted = true;
+    L = pcg_launch_shape(ctx, n, Qw);
+    TRY(plan_iteration());
+    B4 = (const float4*)Bw.p; P4 = (float4*)S.P.p; R4 = (float4*)S.R.p; AP4 = (float4*)S.AP.p;
+    if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] it=%d: %d columns left, working width %d\n", it, active_cols, Kw);
+    phase_report("re-plan");
+    return TCS_OK;
+  };
+  if (opts.column_count > 0 && (opts.column_begin > 0 || opts.column_begin + opts.column_count < K)) {
+    // label-column shard: the other columns count as done from the start
+    int mine = 0;
+    for (int k = 0; k < K; ++k) {
+      if (k < opts.column_begin || k >= opts.column_begin + opts.column_count) done[k] = 1;
+      else ++mine;
+    }
+    if (mine == 0) return tcs_fail(ctx, TCS_ERR_INPUT, "column shard [%d, %d) selects none of the %d colours", opts.column_begin,
+                                   opts.column_begin + opts.column_count, K);
+    const int newKw = std::max(4, (mine + 3) & ~3);
+    if (newKw < Kw) {
+      TRY(compact(newKw, mine));
+    } else {
+      for (int kw = 0; kw < Kw; ++kw)
+        if (wmap[kw] >= 0 && done[wmap[kw]]) h_frozen[kw] = 1;
+      CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+    }
+  }
+  // Every check costs a pass over the float64 solution and a float64 SpMM (8 % of the iterations' time on C4 at one
+  // check per 50 iterations).  While the slowest column is still far from the tolerance - more than a factor
+  // TCS_CHECK_FAR (default 30; 0 = off) above it, i.e. well over a thousand Jacobi-PCG iterations away on these
+  // systems - the next interval is twice check_every.
+  const double far_factor = (double)env_int("TCS_CHECK_FAR", 30);
+  int next_chunk = opts.check_every;
+  // With the hierarchy the solve takes tens of iterations, not thousands, and float32 p / r / Ap put a floor under
+  // the true residual of ONE recurrence (eps32 |A| |x| sqrt(n) / |b|: 2e-5 .. 2e-4 on these systems, measured) - the
+  // recurrence residual keeps falling below it, ever more slowly, while the true one does not move.  So the solve is
+  // classic mixed-precision iterative refinement: a STAGE runs PCG until the recurrence residual of every column
+  // has dropped by `amg_stage` (1e-3) relative to the stage's start (or to the tolerance); then x is folded into
+  // float64, the float64 true residual replaces r, and the next stage starts a fresh direction sequence from it.
+  // Two stages reach 1e-6; a restart costs ~6 iterations (CPU experiment, scripts/amg_lab.py).  Between stage ends
+  // the host only probes the recurrence norms (a 1 KB read every `amg_probe` iterations): nothing disturbs CG.
+  const int amg_probe = std::max(1, env_int("TCS_AMG_PROBE", 4));
+  const double amg_stage = amg::env_double("TCS_AMG_STAGE", 1e-3);
+  const int amg_restart = env_int("TCS_AMG_RESTART", 1);
+  const int amg_x64 = env_int("TCS_AMG_X64", 1);
+  std::vector<double> stage_start((size_t)Kp0, 1.0);
+  if (AH.on) next_chunk = amg_probe;
+  bool replaced = true;    // the last check replaced r: the next step uses the exact line search (it > 0)
+  while (it < opts.max_iterations) {
+    const int chunk = std::min(next_chunk, opts.max_iterations - it);
+    if (coop_grid) {
+      CK(cudaMemsetAsync(coop_bar.p, 0, 4, ctx->stream));
+      int a_n = n, a_Q = Qw, a_chunk = chunk, a_it = it, a_stride = Kp0, a_cap = coop_cap;
+      const uint32_t* a_rowptr = S.rowptr.p;
+      const int* a_col = S.col.p;
+      const float *a_val = S.val.p, *a_diag = S.gdiag.p, *a_invd = invd.p;
+      const float4* a_R = R4;
+      float4* a_Xd = (float4*)Xd.p;
+      const double *a_rz0 = d_rz0, *a_pr = it > 0 ? d_pr : nullptr;
+      const int* a_frozen = frozen.p;
+      double a_done = done_factor;
+      unsigned* a_bar = coop_bar.p;
+      long long* a_dbg = coop_dbg.p;
+      double* a_part = coop_part.p;
+      void* args[] = {&a_n, &a_Q, &a_chunk, &a_it, &a_stride, &a_cap, &a_rowptr, &a_col, &a_val, &a_diag, &a_invd, &P4, &a_R,
+                      &a_Xd, &d_pAp, &d_rz, &a_rz0, &a_pr, &a_frozen, &a_done, &a_bar, &a_part, &a_dbg};
+      const cudaError_t lerr = cudaLaunchCooperativeKernel(coop_fn, dim3(coop_grid), dim3(256), args, coop_smem, ctx->stream);
+      if (lerr == cudaErrorCooperativeLaunchTooLarge || lerr == cudaErrorLaunchOutOfResources) {
+        // the CTAs cannot all be resident right now: this solve continues with one launch per kernel
+        cudaGetLastError();
+        if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] cooperative launch refused (%s): per-kernel path\n", cudaGetErrorString(lerr));
+        // (the refused kernel touched nothing: the accumulators are in the state the per-kernel path expects)
+        coop_grid = 0;
+        coop_disabled = true;
+        TRY(spmm_plan(ctx, S));
+        continue;
+      }
+      CK(lerr);
+      ctx->launches++;
+      if (coop_dbg.p && it == 0) {
+        long long hd[16];
+        CK(cudaMemcpyAsync(hd, coop_dbg.p, sizeof hd, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        for (int b = 0; b < 2; ++b)
+          fprintf(stderr, "[tcs] k_pcg_chunk<%d> grid %u %s CTA, cycles per iteration: spmm %lld reduce %lld barrier %lld | update %lld reduce %lld barrier %lld | dir %lld barrier %lld\n",
+                  coop_M, coop_grid, b ? "last" : "first", hd[8 * b] / chunk, hd[8 * b + 1] / chunk, hd[8 * b + 2] / chunk, hd[8 * b + 3] / chunk,
+                  hd[8 * b + 4] / chunk, hd[8 * b + 5] / chunk, hd[8 * b + 6] / chunk, hd[8 * b + 7] / chunk);
+      }
+      it += chunk;
+      spmm_launches += chunk;
+    } else
+    for (int j = 0; j < chunk; ++j, ++it) {
+      const int s0 = it % 3, s1 = (it + 1) % 3, s2 = (it + 2) % 3;
+      const double* pr = (j == 0 && it > 0 && replaced) ? d_pr : nullptr;  // first step after a residual replacement
+      const bool timed = opts.time_spmm && samples < kMaxSamples && !dropped_columns;
+      if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
+      launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp0);
+      if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
+      ++spmm_launches;
+      LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
+             d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr, AH.on ? d_rr3 + s1 * Kp0 : (double*)nullptr);
+      if (AH.on) TRY(amg::apply(ctx, AH, Qw, R4, d_rz + s1 * Kp0));
+      LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
+             d_pAp + s0 * Kp0, d_rz + s1 * Kp0, d_pAp + s1 * Kp0, d_rz + s2 * Kp0,
+             AH.on ? d_rr3 + s2 * Kp0 : (double*)nullptr, frozen.p, d_rz0, done_factor, pr,
+             AH.on ? amg::fine_agg(AH) : (const uint32_t*)nullptr, AH.on ? amg::result(AH) : (const float4*)nullptr,
+             AH.on ? amg_restart : 0, (AH.on && amg_x64) ? Xw.p : (double*)nullptr);
+    }
+    const size_t nkw = (size_t)n * Kw;
+    bool replace = true;
+    if (AH.on) {
+      // probe: recurrence ||r||^2 of the iteration just queued
+      CK(cudaMemcpyAsync(ctx->h_pin, d_rr3 + (it % 3) * Kp0, (size_t)Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaMemcpyAsync((char*)ctx->h_pin + 512, d_bb, (size_t)Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+      const double* prr = (const double*)ctx->h_pin;
+      const double* pbb = (const double*)((char*)ctx->h_pin + 512);
+      bool stage_open = false;
+      for (int kw = 0; kw < Kw; ++kw)
+        if (wmap[kw] >= 0 && !done[wmap[kw]] && pbb[kw] > 0.0) {
+          const double v = std::sqrt(prr[kw] / pbb[kw]);
+          if (v == v && v > std::max(0.7 * opts.tolerance * seg_scale[kw], amg_stage * stage_start[kw])) stage_open = true;
+        }
+      replaced = false;
+      if (stage_open && it < opts.max_iterations) continue;  // keep iterating, undisturbed
+    }
+    if (replace) {
+      // fold the float32 increment into the float64 solution; the float64 true residual replaces the recurrence
+      // residual, and rz of the coming iteration is recomputed from it
+      LAUNCH(ctx, k_flush_x, div_up(nkw, 256), 256, 0, nkw, Xw.p, Xd.p);
+      CK(cudaMemsetAsync(d_rr, 0, (size_t)Kp0 * 8, ctx->stream));
+      CK(cudaMemsetAsync(d_rz + (it % 3) * Kp0, 0, (size_t)Kp0 * 8, ctx->stream));
+      CK(cudaMemsetAsync(d_pr, 0, (size_t)Kp0 * 8, ctx->stream));
+      if (nseg) {
+        CK(cudaMemsetAsync(seg_rr.p, 0, (size_t)nseg * Kp0 * 8, ctx->stream));
+        for (int sg = 0; sg < nseg; ++sg) {
+          const int r0 = seg->row_begin[sg], nr = seg->row_begin[sg + 1] - r0;
+          if (nr > 0)
+            LAUNCH(ctx, k_true_residual, std::min(L.grid, div_up(nr, 256 / Qw)), L.block, L.smem, r0, nr, Qw, S.rowptr.p, S.col.p,
+                   S.val.p, S.diag.p, B4, Xw.p, P4, R4, seg_rr.p + (size_t)sg * Kp0, d_rz + (it % 3) * Kp0, d_pr);
+        }
+      } else {
+        LAUNCH(ctx, k_true_residual, L.grid, L.block, L.smem, 0, n, Qw, S.rowptr.p, S.col.p, S.val.p, S.diag.p, B4, Xw.p,
+               P4, R4, d_rr, d_rz + (it % 3) * Kp0, d_pr);
+      }
+      if (AH.on) TRY(amg::apply(ctx, AH, Qw, R4, d_rz + (it % 3) * Kp0));
+      CK(cudaMemcpyAsync(ctx->h_pin, d_rr, (size_t)2 * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      if (nseg) CK(cudaMemcpyAsync(h_seg_rr.data(), seg_rr.p, (size_t)nseg * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+      CK(cudaStreamSynchronize(ctx->stream));
+      memcpy(h.data(), ctx->h_pin, (size_t)2 * Kp0 * 8);
+      if (nseg)   // aggregate norms of the batch: what the recurrence probes see
+        for (int kw = 0; kw < Kw; ++kw) {
+          double srr = 0.0, sbb = 0.0;
+          for (int sg = 0; sg < nseg; ++sg) { srr += h_seg_rr[(size_t)sg * Kp0 + kw]; sbb += h_seg_bb[(size_t)sg * Kp0 + kw]; }
+          h[kw] = srr; h[Kp0 + kw] = sbb;
+        }
+      replaced = true;
+    }
+    int active_cols = 0;
+    for (int kw = 0; kw < Kw; ++kw) {
+      const int k = wmap[kw];
+      if (k < 0) continue;
+      const double rr = h[kw], bb = h[Kp0 + kw];
+      const double agg = bb > 0.0 ? std::sqrt(rr / bb) : 0.0;
+      rel[k] = agg;
+      if (nseg) {   // a column is done when the worst SCENE is: the probes see the aggregate, scaled by agg / worst
+        double worst = 0.0;
+        for (int sg = 0; sg < nseg; ++sg) {
+          const double b2 = h_seg_bb[(size_t)sg * Kp0 + kw], r2 = h_seg_rr[(size_t)sg * Kp0 + kw];
+          if (b2 > 0.0) worst = std::max(worst, std::sqrt(r2 / b2));
+        }
+        rel[k] = worst;
+        seg_scale[kw] = (worst > 0.0 && agg > 0.0) ? std::min(1.0, agg / worst) : 1.0;
+      }
+      if (rel[k] <= opts.tolerance) { done[k] = 1; h_frozen[kw] = 1; }
+      if (!done[k]) ++active_cols;
+      stage_start[kw] = agg;
+    }
+    if (getenv("TCS_DEBUG")) {
+      fprintf(stderr, "[tcs] it=%d rel:", it);
+      for (int k = 0; k < K; ++k) fprintf(stderr, " %.2e", rel[k]);
+      fprintf(stderr, "\n");
+    }
+    if (active_cols == 0) { converged = 1; phase_report("done"); break; }
+    {
+      double worst = 0.0;
+      for (int kw = 0; kw < Kw; ++kw)
+        if (wmap[kw] >= 0 && !done[wmap[kw]]) worst = std::max(worst, rel[wmap[kw]]);
+      next_chunk = (far_factor > 0.0 && worst > far_factor * opts.tolerance) ? 2 * opts.check_every : opts.check_every;
+      if (AH.on) next_chunk = amg_probe;
+    }
+    const int newKw = std::max(4, (active_cols + 3) & ~3);
+    if (compact_enabled && newKw < Kw && it < opts.max_iterations) {
+      TRY(compact(newKw, active_cols));
+      dropped_columns = true;
+    } else {
+      CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+  }
+  if (opts.column_count > 0)
+    for (int k = 0; k < K; ++k)
+      if (k < opts.column_begin || k >= opts.column_begin + opts.column_count) rel[k] = 0.0;  // not this shard's
+  // the float64 solution of all columns, n x Kp0
+  if (!compacted) {
+    S.X.swap(Xw);
+  } else {
+    std::vector<int> cols(2 * (size_t)Kp0, -1);
+    for (int kw = 0; kw < Kw; ++kw) cols[kw] = wmap[kw];
+    CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
+    const size_t nkw = (size_t)n * Kw;
+    LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
+    CK(cudaStreamSynchronize(ctx->stream));
+    // the SpMM plan and P belong to the narrow working set: the measurement hooks re-plan at full width
+    S.Kp = Kp0;
+    S.ring = S.tiled = false;
+    S.plan_stale = true;
+    S.P.release();
+  }
+  iterations = it;
+  for (int sidx = 0; sidx < samples; ++sidx) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, evs[2 * sidx], evs[2 * sidx + 1]));
+    spmm_sum_ms += ms;
+    ++spmm_timed;
+  }
+  for (auto& e : evs) cudaEventDestroy(e);
+  // the work vectors are only needed again by tcs_bench_spmm, which re-allocates them
+  S.R.release(); S.AP.release();
+  res.iterations = iterations;
+  res.converged = converged;
+  for (int k = 0; k < K; ++k) res.rel[k] = rel[k];
+  res.spmm_launches = spmm_launches;
+  res.kernel = kernel_at_start;  // the kernel planned for the full label block
+  res.spmm_ms = spmm_timed ? spmm_sum_ms / spmm_timed * spmm_launches : 0.f;
+  return TCS_OK;
+}
+
+// assignColors + getPotentials for `nrows` rows of a solved system (X: their nrows x Kp float64 solution, row_vertex:
+// their vertices): labels into g->colours, best potentials into g->best_val, near-tie count into info
+int tcs_impl_argmax(tcs_graph* g, const uint32_t* row_vertex, int nrows, int K, int Kp, const double* X,
+                    const tcs_solver_opts& opts, float* d_pot, tcs_solve_info* info) {
+  tcs_ctx* ctx = g->ctx;
+  TRY(g->best_val.alloc(ctx, g->V));
+  if (g->V) LAUNCH(ctx, k_best_init, div_up(g->V, 256), 256, 0, g->V, g->colours.p, g->best_val.p);
+  DBuf<unsigned long long> ties;
+  TRY(ties.alloc(ctx, 1));
+  CK(cudaMemsetAsync(ties.p, 0, 8, ctx->stream));
+  int k0 = 0, k1 = K;
+  if (opts.column_count > 0) { k0 = std::max(0, opts.column_begin); k1 = std::min(K, opts.column_begin + opts.column_count); }
+  if (nrows > 0)
+    LAUNCH(ctx, k_argmax, div_up(nrows, 256), 256, 0, nrows, K, Kp, k0, k1, X, row_vertex, g->colours.p, d_pot, g->V, ties.p,
+           g->best_val.p);
+  if (info) {
+    CK(cudaMemcpyAsync(ctx->h_pin, ties.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    info->near_ties = (long long)*(unsigned long long*)ctx->h_pin;
+  }
+  return TCS_OK;
+}
+
 int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, tcs_solve_info* info) {
   tcs_ctx* ctx = g->ctx;
   tcs_solver_opts opts;
@@ -1053,12 +1558,8 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
   TRY(tcs_impl_assemble(g, K));
   CK(cudaEventRecord(e_asm1, ctx->stream));
   tcs_system& S = g->sys;
-  const int n = S.n, Kp = S.Kp, Q = Kp / 4;
+  const int n = S.n;
   if (info) { info->rows = n; info->nnz = S.nnz_off + n; }
-  if (n > 0) {
-    TRY(S.gdiag.alloc(ctx, (size_t)n + 8));
-    LAUNCH(ctx, k_diag_excess, div_up(n, 256), 256, 0, n, S.rowptr.p, S.val.p, S.diag.p, S.gdiag.p);
-  }
 
   float* d_pot = nullptr;
   if (opts.store_potentials) {
@@ -1072,428 +1573,34 @@ int tcs_impl_random_walker(tcs_graph* g, int K, const tcs_solver_opts* opts_in, 
     g->pot_K = 0;
   }
 
-  TRY(g->best_val.alloc(ctx, V));
-  LAUNCH(ctx, k_best_init, div_up(V, 256), 256, 0, V, g->colours.p, g->best_val.p);
-  int iterations = 0, converged = 1, kernel_at_start = 0;
-  double rel[TCS_MAX_LABELS] = {0};
-  float spmm_sum_ms = 0.f;
-  int spmm_timed = 0, spmm_launches = 0;
+  tcs_pcg_result res;
+  if (n == 0) {   // every vertex is a seed or isolated: the labels are the seeds
+    TRY(g->best_val.alloc(ctx, V));
+    LAUNCH(ctx, k_best_init, div_up(V, 256), 256, 0, V, g->colours.p, g->best_val.p);
+  }
   if (n > 0) {
-    // Working set: the label columns still iterating, packed to a multiple of 4.  wmap[kw] = original column of working
-    // column kw (-1 = padding).  Columns are independent systems (one right-hand side each): when enough of them
-    // have reached the tolerance to drop a float4 of columns, the survivors are re-packed and the SpMM re-planned
-    // for the narrower rows, so converged columns stop costing bandwidth (C4: 6 of 16 columns finish within 700 of
-    // 8050 iterations).  TCS_COMPACT=0 keeps all columns (they are then frozen instead).
-    const int Kp0 = Kp;
-    int Kw = Kp0, Qw = Q;
-    std::vector<int> wmap(Kw);
-    for (int k = 0; k < Kw; ++k) wmap[k] = k < K ? k : -1;
-    std::vector<char> done(K, 0);
-    bool compact_enabled = env_int("TCS_COMPACT", 1) != 0;
-    bool compacted = false;
-    bool dropped_columns = false;  // converged columns have left the working set (SpMM timing samples stop there)
-    const size_t nk = (size_t)n * Kp0;
-    DBuf<double> Xw;   // float64 solution of the working columns (becomes S.X when no compaction happens)
-    DBuf<float> Xd;    // float32 increment since the last flush
-    DBuf<float> Bw;    // right-hand sides of the working columns (S.B itself until the first compaction)
-    S.X.release();
-    TRY(Xw.alloc(ctx, nk)); TRY(Xd.alloc(ctx, nk));
-    TRY(S.P.alloc(ctx, nk)); TRY(S.R.alloc(ctx, nk)); TRY(S.AP.alloc(ctx, nk));
-    DBuf<float> invd;
-    TRY(invd.alloc(ctx, n));
-    // scalar accumulators, row stride Kp0: pAp[3], rz[3], rr, bb, rz of the initial residual, p.r, recurrence rr[3]
-    const int kScalRows = 13;
-    DBuf<double> scal;
-    TRY(scal.alloc(ctx, (size_t)kScalRows * Kp0));
-    CK(cudaMemsetAsync(scal.p, 0, (size_t)kScalRows * Kp0 * 8, ctx->stream));
-    double* d_pAp = scal.p;
-    double* d_rz = scal.p + 3 * Kp0;
-    double* d_rr = scal.p + 6 * Kp0;
-    double* d_bb = scal.p + 7 * Kp0;
-    double* d_rz0 = scal.p + 8 * Kp0;
-    double* d_pr = scal.p + 9 * Kp0;   // p . r of the last residual replacement
-    double* d_rr3 = scal.p + 10 * Kp0; // ||r||^2 of the recurrence residual (three generations, like rz)
-    // device-side "done": recurrence residual four decades below the tolerance (in the D^-1 norm, relative to b) -
-    // far from the tolerance itself (the two norms differ), far above float32 underflow of r
-    const double done_factor = 1e-8 * opts.tolerance * opts.tolerance;
-    DBuf<int> frozen, d_cols;
-    TRY(frozen.alloc(ctx, Kp0)); TRY(d_cols.alloc(ctx, 2 * (size_t)Kp0));
-    CK(cudaMemsetAsync(frozen.p, 0, (size_t)Kp0 * 4, ctx->stream));
-    int* h_frozen = (int*)((char*)ctx->h_pin + 2048);
-    for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
-    PcgLaunch L = pcg_launch_shape(ctx, n, Qw);
-    // small systems: whole chunks of iterations in one persistent cooperative launch (k_pcg_chunk) instead of three
-    // launches per iteration; no SpMM plan is needed then (the measurement hooks plan on demand)
-    DBuf<unsigned> coop_bar;
-    DBuf<double> coop_part;     // per-CTA partial dot products
-    DBuf<long long> coop_dbg;   // TCS_DEBUG: cycles per phase of the first and the last CTA
-    TRY(coop_bar.alloc(ctx, 1));
-    if (getenv("TCS_DEBUG")) TRY(coop_dbg.alloc(ctx, 16));
-    unsigned coop_grid = 0;
-    bool coop_disabled = false;
-    int coop_M = 0, coop_cap = 0;
-    size_t coop_smem = 0;
-    const void* coop_fn = nullptr;
-    auto plan_iteration = [&]() -> int {
-      coop_grid = 0;
-      const int rows_per_block = 256 / Qw;
-      const int ntiles = (n + rows_per_block - 1) / rows_per_block;
-      // at most 4 row tiles per CTA, all CTAs co-resident: n * Q <= ~1.2 M (a 640 x 480 scene with 16 labels is 0.2 M)
-      if (!coop_disabled && env_int("TCS_COOP", 1) != 0 && !opts.time_spmm && !getenv("TCS_SPMM") && ntiles <= 4 * 8 * ctx->sm_count &&
-          n <= env_int("TCS_COOP_MAX_ROWS", 100000)) {
-        uint32_t* d_max = (uint32_t*)ctx->d_scal + 16;
-        CK(cudaMemsetAsync(d_max, 0, 4, ctx->stream));
-        LAUNCH(ctx, k_tile_max_nnz, div_up(ntiles, 256), 256, 0, n, rows_per_block, S.rowptr.p, d_max);
-        uint32_t mx = 0;
-        TRY(tcs_impl_read_u32(ctx, d_max, &mx));
-        const int cap = (int)((mx + 1u) & ~1u);
-        const void* fns[4] = {(const void*)k_pcg_chunk<1>, (const void*)k_pcg_chunk<2>, (const void*)k_pcg_chunk<3>,
-                              (const void*)k_pcg_chunk<4>};
-        const int max_ctas = env_int("TCS_COOP_CTAS", 8);
-        for (int M = 1; M <= 4; ++M) {
-          const size_t smem = (size_t)M * cap * 8 + 256 * 4 * 8 + (size_t)Kw * (4 * 8 + 3 * 4);
-          if (smem > 200 * 1024) break;
-          // always the same value: function attributes are shared by every host thread that drives this device
-          if (cudaFuncSetAttribute(fns[M - 1], cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) {
-            cudaGetLastError();
-            break;
-          }
-          int nb = 0;
-          if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fns[M - 1], 256, smem) != cudaSuccess || nb < 1) { cudaGetLastError(); break; }
-          const int resident = ctx->sm_count * std::min(nb, max_ctas);
-          const int grid = (ntiles + M - 1) / M;
-          if (grid > resident) continue;
-          coop_grid = (unsigned)grid; coop_M = M; coop_cap = cap; coop_smem = smem; coop_fn = fns[M - 1];
-          if (getenv("TCS_DEBUG"))
-            fprintf(stderr, "[tcs] chunk plan: n=%d Q=%d tiles=%d cap=%d M=%d grid=%d smem=%zu occupancy=%d\n", n, Qw, ntiles, cap, M, grid, smem, nb);
-          TRY(coop_part.alloc(ctx, 2 * (size_t)grid * Kw));
-          S.ring = S.tiled = false;
-          S.plan_stale = true;
-          return TCS_OK;
-        }
-      }
-      return spmm_plan(ctx, S);
-    };
-    {
-      const unsigned sleep_ns = (unsigned)env_int("TCS_COOP_SLEEP", 0);
-      CK(cudaMemcpyToSymbolAsync(c_coop_sleep, &sleep_ns, 4, 0, cudaMemcpyHostToDevice, ctx->stream));
-      CK(cudaStreamSynchronize(ctx->stream));
-    }
-    // coarse levels of the preconditioner (amg.cuh); with them the solve runs on the per-kernel path
-    amg::Hierarchy AH;
-    TRY(amg::setup(ctx, S, Kp0, AH));
-    if (AH.on) {
-      coop_disabled = true;
-      // a few dozen iterations in all: re-planning the SpMM for a narrower working set costs more than it saves
-      if (!getenv("TCS_COMPACT")) compact_enabled = false;
-    }
-    TRY(plan_iteration());
-    kernel_at_start = coop_grid ? 4 : S.ring ? 3 : S.tiled ? 2 : 1;
-    const float4* B4 = (const float4*)S.B.p;
-    float4* P4 = (float4*)S.P.p;
-    float4* R4 = (float4*)S.R.p;
-    float4* AP4 = (float4*)S.AP.p;
-    LAUNCH(ctx, k_pcg_init, L.grid, L.block, L.smem, n, Qw, B4, S.diag.p, invd.p, R4, P4, Xw.p, (float4*)Xd.p, d_rz, d_bb);
-    if (AH.on) {
-      TRY(amg::apply(ctx, AH, Qw, R4, d_rz));
-      LAUNCH(ctx, amg::k_prolong, div_up((size_t)n * Qw, 256), 256, 0, n, Qw, 1.0f, amg::fine_agg(AH), amg::result(AH), P4);
-    }
-    CK(cudaMemcpyAsync(d_rz0, d_rz, (size_t)Kp0 * 8, cudaMemcpyDeviceToDevice, ctx->stream));
-    std::vector<double> h((size_t)kScalRows * Kp0);
-    // sampled SpMM timing: one event pair per launch for the first launches (full width)
-    const int kMaxSamples = 64;
-    std::vector<cudaEvent_t> evs;
-    if (opts.time_spmm) {
-      evs.resize(2 * kMaxSamples);
-      for (auto& e : evs) CK(cudaEventCreate(&e));
-    }
-    int samples = 0;
-    converged = 0;
-    int it = 0;
-    // TCS_DEBUG: wall-clock per phase (we synchronise at every check, so host time brackets device time)
-    auto phase_t0 = std::chrono::steady_clock::now();
-    int phase_it0 = 0;
-    auto phase_report = [&](const char* what) {
-      if (!getenv("TCS_DEBUG")) return;
-      const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - phase_t0).count();
-      fprintf(stderr, "[tcs] %s: iterations %d..%d at width %d, kernel %d: %.1f ms = %.1f us / iteration\n", what, phase_it0, it,
-              Kw, S.ring ? 3 : S.tiled ? 2 : 1, ms, it > phase_it0 ? 1e3 * ms / (it - phase_it0) : 0.0);
-      phase_t0 = std::chrono::steady_clock::now();
-      phase_it0 = it;
-    };
-    // ---- re-pack the working set to the columns that are not done (newKw = their count rounded up to 4)
-    auto compact = [&](int newKw, int active_cols) -> int {
-      const size_t nkw = (size_t)n * Kw;
-      // ---- drop the converged columns
-      phase_report("compaction");
-      if (!S.X.p) {
-        TRY(S.X.alloc(ctx, nk));
-        CK(cudaMemsetAsync(S.X.p, 0, nk * 8, ctx->stream));
-      }
-      std::vector<int> cols(2 * (size_t)Kp0, -1), newmap;  // [0, Kp0): scatter targets; [Kp0, 2 Kp0): repack sources
-      for (int kw = 0; kw < Kw; ++kw) {
-        cols[kw] = wmap[kw];
-        if (wmap[kw] >= 0 && !done[wmap[kw]]) { cols[Kp0 + newmap.size()] = kw; newmap.push_back(wmap[kw]); }
-      }
-      newmap.resize(newKw, -1);
-      CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
-      LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
-      const size_t nk2 = (size_t)n * newKw;
-      DBuf<float> P2, R2, B2, Xd2, AP2;
-      DBuf<double> X2;
-      TRY(P2.alloc(ctx, nk2)); TRY(R2.alloc(ctx, nk2)); TRY(B2.alloc(ctx, nk2)); TRY(Xd2.alloc(ctx, nk2));
-      TRY(AP2.alloc(ctx, nk2)); TRY(X2.alloc(ctx, nk2));
-      const int* src = d_cols.p + Kp0;
-      LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.P.p, P2.p);
-      LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, S.R.p, R2.p);
-      LAUNCH(ctx, k_repack_columns<float>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src,
-             Bw.p ? Bw.p : S.B.p, B2.p);
-      LAUNCH(ctx, k_repack_columns<double>, div_up(nk2, 256), 256, 0, (size_t)n, Kw, newKw, src, Xw.p, X2.p);
-      CK(cudaMemsetAsync(Xd2.p, 0, nk2 * 4, ctx->stream));
-      // per-column scalars: same permutation on the host (we are at a synchronisation point anyway)
-      CK(cudaMemcpyAsync(h.data(), scal.p, (size_t)kScalRows * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
-      CK(cudaStreamSynchronize(ctx->stream));  // also: `cols` was read by the copy above
-      std::vector<double> h2((size_t)kScalRows * Kp0, 0.0);
-      for (int r8 = 0; r8 < kScalRows; ++r8)
-        for (int k2 = 0; k2 < newKw; ++k2)
-          if (cols[Kp0 + k2] >= 0) h2[(size_t)r8 * Kp0 + k2] = h[(size_t)r8 * Kp0 + cols[Kp0 + k2]];
-      CK(cudaMemcpyAsync(scal.p, h2.data(), (size_t)kScalRows * Kp0 * 8, cudaMemcpyHostToDevice, ctx->stream));
-      for (int k = 0; k < Kp0; ++k) h_frozen[k] = 0;
-      CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
-      CK(cudaStreamSynchronize(ctx->stream));  // h2 is a local vector
-      S.P.swap(P2); S.R.swap(R2); S.AP.swap(AP2); Bw.swap(B2); Xw.swap(X2); Xd.swap(Xd2);
-      Kw = newKw; Qw = Kw / 4; wmap = newmap;
-      S.Kp = Kw;
-      compacted = true;
-      L = pcg_launch_shape(ctx, n, Qw);
-      TRY(plan_iteration());
-      B4 = (const float4*)Bw.p; P4 = (float4*)S.P.p; R4 = (float4*)S.R.p; AP4 = (float4*)S.AP.p;
-      if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] it=%d: %d columns left, working width %d\n", it, active_cols, Kw);
-      phase_report("re-plan");
-      return TCS_OK;
-    };
-    if (opts.column_count > 0 && (opts.column_begin > 0 || opts.column_begin + opts.column_count < K)) {
-      // label-column shard: the other columns count as done from the start
-      int mine = 0;
-      for (int k = 0; k < K; ++k) {
-        if (k < opts.column_begin || k >= opts.column_begin + opts.column_count) done[k] = 1;
-        else ++mine;
-      }
-      if (mine == 0) return tcs_fail(ctx, TCS_ERR_INPUT, "column shard [%d, %d) selects none of the %d colours", opts.column_begin,
-                                     opts.column_begin + opts.column_count, K);
-      const int newKw = std::max(4, (mine + 3) & ~3);
-      if (newKw < Kw) {
-        TRY(compact(newKw, mine));
-      } else {
-        for (int kw = 0; kw < Kw; ++kw)
-          if (wmap[kw] >= 0 && done[wmap[kw]]) h_frozen[kw] = 1;
-        CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-      }
-    }
-    // Every check costs a pass over the float64 solution and a float64 SpMM (8 % of the iterations' time on C4 at one
-    // check per 50 iterations).  While the slowest column is still far from the tolerance - more than a factor
-    // TCS_CHECK_FAR (default 30; 0 = off) above it, i.e. well over a thousand Jacobi-PCG iterations away on these
-    // systems - the next interval is twice check_every.
-    const double far_factor = (double)env_int("TCS_CHECK_FAR", 30);
-    int next_chunk = opts.check_every;
-    // With the hierarchy the solve takes tens of iterations, not thousands, and float32 p / r / Ap put a floor under
-    // the true residual of ONE recurrence (eps32 |A| |x| sqrt(n) / |b|: 2e-5 .. 2e-4 on these systems, measured) - the
-    // recurrence residual keeps falling below it, ever more slowly, while the true one does not move.  So the solve is
-    // classic mixed-precision iterative refinement: a STAGE runs PCG until the recurrence residual of every column
-    // has dropped by `amg_stage` (1e-3) relative to the stage's start (or to the tolerance); then x is folded into
-    // float64, the float64 true residual replaces r, and the next stage starts a fresh direction sequence from it.
-    // Two stages reach 1e-6; a restart costs ~6 iterations (CPU experiment, scripts/amg_lab.py).  Between stage ends
-    // the host only probes the recurrence norms (a 1 KB read every `amg_probe` iterations): nothing disturbs CG.
-    const int amg_probe = std::max(1, env_int("TCS_AMG_PROBE", 4));
-    const double amg_stage = amg::env_double("TCS_AMG_STAGE", 1e-3);
-    const int amg_restart = env_int("TCS_AMG_RESTART", 1);
-    const int amg_x64 = env_int("TCS_AMG_X64", 1);
-    std::vector<double> stage_start((size_t)Kp0, 1.0);
-    if (AH.on) next_chunk = amg_probe;
-    bool replaced = true;    // the last check replaced r: the next step uses the exact line search (it > 0)
-    while (it < opts.max_iterations) {
-      const int chunk = std::min(next_chunk, opts.max_iterations - it);
-      if (coop_grid) {
-        CK(cudaMemsetAsync(coop_bar.p, 0, 4, ctx->stream));
-        int a_n = n, a_Q = Qw, a_chunk = chunk, a_it = it, a_stride = Kp0, a_cap = coop_cap;
-        const uint32_t* a_rowptr = S.rowptr.p;
-        const int* a_col = S.col.p;
-        const float *a_val = S.val.p, *a_diag = S.gdiag.p, *a_invd = invd.p;
-        const float4* a_R = R4;
-        float4* a_Xd = (float4*)Xd.p;
-        const double *a_rz0 = d_rz0, *a_pr = it > 0 ? d_pr : nullptr;
-        const int* a_frozen = frozen.p;
-        double a_done = done_factor;
-        unsigned* a_bar = coop_bar.p;
-        long long* a_dbg = coop_dbg.p;
-        double* a_part = coop_part.p;
-        void* args[] = {&a_n, &a_Q, &a_chunk, &a_it, &a_stride, &a_cap, &a_rowptr, &a_col, &a_val, &a_diag, &a_invd, &P4, &a_R,
-                        &a_Xd, &d_pAp, &d_rz, &a_rz0, &a_pr, &a_frozen, &a_done, &a_bar, &a_part, &a_dbg};
-        const cudaError_t lerr = cudaLaunchCooperativeKernel(coop_fn, dim3(coop_grid), dim3(256), args, coop_smem, ctx->stream);
-        if (lerr == cudaErrorCooperativeLaunchTooLarge || lerr == cudaErrorLaunchOutOfResources) {
-          // the CTAs cannot all be resident right now: this solve continues with one launch per kernel
-          cudaGetLastError();
-          if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] cooperative launch refused (%s): per-kernel path\n", cudaGetErrorString(lerr));
-          // (the refused kernel touched nothing: the accumulators are in the state the per-kernel path expects)
-          coop_grid = 0;
-          coop_disabled = true;
-          TRY(spmm_plan(ctx, S));
-          continue;
-        }
-        CK(lerr);
-        ctx->launches++;
-        if (coop_dbg.p && it == 0) {
-          long long hd[16];
-          CK(cudaMemcpyAsync(hd, coop_dbg.p, sizeof hd, cudaMemcpyDeviceToHost, ctx->stream));
-          CK(cudaStreamSynchronize(ctx->stream));
-          for (int b = 0; b < 2; ++b)
-            fprintf(stderr, "[tcs] k_pcg_chunk<%d> grid %u %s CTA, cycles per iteration: spmm %lld reduce %lld barrier %lld | update %lld reduce %lld barrier %lld | dir %lld barrier %lld\n",
-                    coop_M, coop_grid, b ? "last" : "first", hd[8 * b] / chunk, hd[8 * b + 1] / chunk, hd[8 * b + 2] / chunk, hd[8 * b + 3] / chunk,
-                    hd[8 * b + 4] / chunk, hd[8 * b + 5] / chunk, hd[8 * b + 6] / chunk, hd[8 * b + 7] / chunk);
-        }
-        it += chunk;
-        spmm_launches += chunk;
-      } else
-      for (int j = 0; j < chunk; ++j, ++it) {
-        const int s0 = it % 3, s1 = (it + 1) % 3, s2 = (it + 2) % 3;
-        const double* pr = (j == 0 && it > 0 && replaced) ? d_pr : nullptr;  // first step after a residual replacement
-        const bool timed = opts.time_spmm && samples < kMaxSamples && !dropped_columns;
-        if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
-        launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp0);
-        if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
-        ++spmm_launches;
-        LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
-               d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr, AH.on ? d_rr3 + s1 * Kp0 : (double*)nullptr);
-        if (AH.on) TRY(amg::apply(ctx, AH, Qw, R4, d_rz + s1 * Kp0));
-        LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
-               d_pAp + s0 * Kp0, d_rz + s1 * Kp0, d_pAp + s1 * Kp0, d_rz + s2 * Kp0,
-               AH.on ? d_rr3 + s2 * Kp0 : (double*)nullptr, frozen.p, d_rz0, done_factor, pr,
-               AH.on ? amg::fine_agg(AH) : (const uint32_t*)nullptr, AH.on ? amg::result(AH) : (const float4*)nullptr,
-               AH.on ? amg_restart : 0, (AH.on && amg_x64) ? Xw.p : (double*)nullptr);
-      }
-      const size_t nkw = (size_t)n * Kw;
-      bool replace = true;
-      if (AH.on) {
-        // probe: recurrence ||r||^2 of the iteration just queued
-        CK(cudaMemcpyAsync(ctx->h_pin, d_rr3 + (it % 3) * Kp0, (size_t)Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync((char*)ctx->h_pin + 512, d_bb, (size_t)Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        const double* prr = (const double*)ctx->h_pin;
-        const double* pbb = (const double*)((char*)ctx->h_pin + 512);
-        bool stage_open = false;
-        for (int kw = 0; kw < Kw; ++kw)
-          if (wmap[kw] >= 0 && !done[wmap[kw]] && pbb[kw] > 0.0) {
-            const double v = std::sqrt(prr[kw] / pbb[kw]);
-            if (v == v && v > std::max(0.7 * opts.tolerance, amg_stage * stage_start[kw])) stage_open = true;
-          }
-        replaced = false;
-        if (stage_open && it < opts.max_iterations) continue;  // keep iterating, undisturbed
-      }
-      if (replace) {
-        // fold the float32 increment into the float64 solution; the float64 true residual replaces the recurrence
-        // residual, and rz of the coming iteration is recomputed from it
-        LAUNCH(ctx, k_flush_x, div_up(nkw, 256), 256, 0, nkw, Xw.p, Xd.p);
-        CK(cudaMemsetAsync(d_rr, 0, (size_t)Kp0 * 8, ctx->stream));
-        CK(cudaMemsetAsync(d_rz + (it % 3) * Kp0, 0, (size_t)Kp0 * 8, ctx->stream));
-        CK(cudaMemsetAsync(d_pr, 0, (size_t)Kp0 * 8, ctx->stream));
-        LAUNCH(ctx, k_true_residual, L.grid, L.block, L.smem, n, Qw, S.rowptr.p, S.col.p, S.val.p, S.diag.p, B4, Xw.p,
-               P4, R4, d_rr, d_rz + (it % 3) * Kp0, d_pr);
-        if (AH.on) TRY(amg::apply(ctx, AH, Qw, R4, d_rz + (it % 3) * Kp0));
-        CK(cudaMemcpyAsync(ctx->h_pin, d_rr, (size_t)2 * Kp0 * 8, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        memcpy(h.data(), ctx->h_pin, (size_t)2 * Kp0 * 8);
-        replaced = true;
-      }
-      int active_cols = 0;
-      for (int kw = 0; kw < Kw; ++kw) {
-        const int k = wmap[kw];
-        if (k < 0) continue;
-        const double rr = h[kw], bb = h[Kp0 + kw];
-        rel[k] = bb > 0.0 ? std::sqrt(rr / bb) : 0.0;
-        if (rel[k] <= opts.tolerance) { done[k] = 1; h_frozen[kw] = 1; }
-        if (!done[k]) ++active_cols;
-        stage_start[kw] = rel[k];
-      }
-      if (getenv("TCS_DEBUG")) {
-        fprintf(stderr, "[tcs] it=%d rel:", it);
-        for (int k = 0; k < K; ++k) fprintf(stderr, " %.2e", rel[k]);
-        fprintf(stderr, "\n");
-      }
-      if (active_cols == 0) { converged = 1; phase_report("done"); break; }
-      {
-        double worst = 0.0;
-        for (int kw = 0; kw < Kw; ++kw)
-          if (wmap[kw] >= 0 && !done[wmap[kw]]) worst = std::max(worst, rel[wmap[kw]]);
-        next_chunk = (far_factor > 0.0 && worst > far_factor * opts.tolerance) ? 2 * opts.check_every : opts.check_every;
-        if (AH.on) next_chunk = amg_probe;
-      }
-      const int newKw = std::max(4, (active_cols + 3) & ~3);
-      if (compact_enabled && newKw < Kw && it < opts.max_iterations) {
-        TRY(compact(newKw, active_cols));
-        dropped_columns = true;
-      } else {
-        CK(cudaMemcpyAsync(frozen.p, h_frozen, (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
-      }
-    }
-    if (opts.column_count > 0)
-      for (int k = 0; k < K; ++k)
-        if (k < opts.column_begin || k >= opts.column_begin + opts.column_count) rel[k] = 0.0;  // not this shard's
-    // the float64 solution of all columns, n x Kp0
-    if (!compacted) {
-      S.X.swap(Xw);
-    } else {
-      std::vector<int> cols(2 * (size_t)Kp0, -1);
-      for (int kw = 0; kw < Kw; ++kw) cols[kw] = wmap[kw];
-      CK(cudaMemcpyAsync(d_cols.p, cols.data(), 2 * (size_t)Kp0 * 4, cudaMemcpyHostToDevice, ctx->stream));
-      const size_t nkw = (size_t)n * Kw;
-      LAUNCH(ctx, k_scatter_columns, div_up(nkw, 256), 256, 0, (size_t)n, Kw, Kp0, d_cols.p, Xw.p, S.X.p);
-      CK(cudaStreamSynchronize(ctx->stream));
-      // the SpMM plan and P belong to the narrow working set: the measurement hooks re-plan at full width
-      S.Kp = Kp0;
-      S.ring = S.tiled = false;
-      S.plan_stale = true;
-      S.P.release();
-    }
-    iterations = it;
+    TRY(tcs_impl_pcg_solve(ctx, S, K, opts, nullptr, res));
     CK(cudaEventRecord(e_solve1, ctx->stream));
-    DBuf<unsigned long long> ties;
-    TRY(ties.alloc(ctx, 1));
-    CK(cudaMemsetAsync(ties.p, 0, 8, ctx->stream));
-    int k0 = 0, k1 = K;
-    if (opts.column_count > 0) { k0 = std::max(0, opts.column_begin); k1 = std::min(K, opts.column_begin + opts.column_count); }
-    LAUNCH(ctx, k_argmax, div_up(n, 256), 256, 0, n, K, Kp, k0, k1, S.X.p, S.row_vertex.p, g->colours.p, d_pot, V, ties.p,
-           g->best_val.p);
+    TRY(tcs_impl_argmax(g, S.row_vertex.p, n, K, S.Kp, S.X.p, opts, d_pot, info));
     CK(cudaEventRecord(e_arg1, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->h_pin, ties.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    if (info) info->near_ties = (long long)*(unsigned long long*)ctx->h_pin;
-    for (int sidx = 0; sidx < samples; ++sidx) {
-      float ms = 0.f;
-      CK(cudaEventElapsedTime(&ms, evs[2 * sidx], evs[2 * sidx + 1]));
-      spmm_sum_ms += ms;
-      ++spmm_timed;
-    }
-    for (auto& e : evs) cudaEventDestroy(e);
     if (info) {
       float ms = 0.f;
       CK(cudaEventElapsedTime(&ms, e_asm0, e_asm1)); info->stage_ms[8] = ms;
       CK(cudaEventElapsedTime(&ms, e_asm1, e_solve1)); info->stage_ms[9] = ms; info->solve_ms = ms;
       CK(cudaEventElapsedTime(&ms, e_solve1, e_arg1)); info->stage_ms[10] = ms;
     }
-    // the work vectors are only needed again by tcs_bench_spmm, which re-allocates them
-    S.R.release(); S.AP.release();
   }
   if (info) {
-    info->iterations = iterations;
-    info->converged = converged;
-    for (int k = 0; k < K; ++k) info->rel_residual[k] = rel[k];
-    info->spmm_launches = spmm_launches;
-    info->spmm_kernel = kernel_at_start;  // the kernel planned for the full label block
-    info->spmm_ms = spmm_timed ? spmm_sum_ms / spmm_timed * spmm_launches : 0.f;
+    info->iterations = res.iterations;
+    info->converged = res.converged;
+    for (int k = 0; k < K; ++k) info->rel_residual[k] = res.rel[k];
+    info->spmm_launches = res.spmm_launches;
+    info->spmm_kernel = res.kernel;
+    info->spmm_ms = res.spmm_ms;
   }
   CK(cudaGetLastError());
-  if (!converged) return tcs_fail(ctx, TCS_ERR_NOT_CONVERGED, "PCG did not reach %.1e in %d iterations", opts.tolerance, iterations);
+  if (!res.converged) return tcs_fail(ctx, TCS_ERR_NOT_CONVERGED, "PCG did not reach %.1e in %d iterations", opts.tolerance, res.iterations);
   return TCS_OK;
 }
 

