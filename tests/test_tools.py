@@ -144,7 +144,9 @@ def test_app_matches_oracle_and_scores(scenes, tmp_path, name, res):
     finite = np.isfinite(xyz).all(axis=1)
     expect, _ = _expected_errors(label.astype(np.int64), got["label"].astype(np.int64), finite)
     assert int(re.search(r"Erroneous points: (\d+)", r.stdout).group(1)) == expect
-    assert expect < 0.05 * finite.sum()               # 5 seeds per label segment these scenes to > 95 %
+    # plausibility only (the labels equal the oracle's, checked above, so this is the reference algorithm's own score
+    # with 5 seeds per label): 0.2 - 3 % erroneous points on the 3..9-label scenes, 5.7 % on the 18-label test56
+    assert expect < 0.08 * finite.sum()
 
 
 @pytest.mark.gpu
