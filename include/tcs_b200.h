@@ -161,6 +161,18 @@ int tcs_components(tcs_graph* g, int* ncomponents, int32_t* component);
 void tcs_solver_opts_default(tcs_solver_opts* o);
 /* seed -> nearest vertex (pcl::getApproximateIndices, impl/random_walker_segmentation.hpp:149-152) */
 int tcs_nearest_vertices(tcs_graph* g, const float* seed_xyz, size_t ns, int32_t* out);
+/* Allocation-free variant of tcs_nearest_vertices.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same inputs, outputs and results as tcs_nearest_vertices (bit-identical: same distance arithmetic,
+ * ties -> lowest vertex id), but every device buffer it needs (seed staging, per-(seed, chunk) partial minima, the
+ * result) lives in ONE fixed file-scope device array of 276 KB that every GPU loading the library holds until exit; it
+ * calls no cudaMalloc / cudaFree / allocating library routine.  Limits and rules:
+ *  - ns <= TCS_NOALLOC_MAX_SEEDS, otherwise TCS_ERR_INPUT with a message (use tcs_nearest_vertices for more);
+ *  - all calls on one GPU share the array, which keeps the last call's contents (every slot a call reads is written
+ *    by that call first); calls that overlap on the GPU - different contexts / streams - RACE: serialise them;
+ *  - ns = 0 only resolves the array's device address (once per device): call it once before a graph capture. */
+#define TCS_NOALLOC_MAX_SEEDS 1024
+int tcs_nearest_vertices_noalloc(tcs_graph* g, const float* seed_xyz, size_t ns, int32_t* out);
 /* randomWalker(graph, weights, colours[, potentials, colour->column]) (random_walker.h:95-137,
  * impl/random_walker.hpp:95-243) on all connected components at once.
  * colours: V uint32; in: seed colours 1..ncolours (0 = unlabelled); out: labels.

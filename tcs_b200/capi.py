@@ -20,6 +20,7 @@ MODE_PARITY, MODE_FAST = 0, 1
 PRESET_CLASS, PRESET_CLI = 0, 1
 OK, ERR_CUDA, ERR_INPUT, ERR_DEPTH, ERR_NOT_CONVERGED, ERR_STATE = 0, -1, -2, -3, -4, -5
 MAX_LABELS = 64
+NOALLOC_MAX_SEEDS = 1024
 NIL = 0xFFFFFFFF
 
 # weight presets
@@ -38,7 +39,7 @@ EXPORTS = [
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
     "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm", "tcs_graph_download_best",
-    "tcs_build_nn_graph", "tcs_segment_batch",
+    "tcs_build_nn_graph", "tcs_segment_batch", "tcs_nearest_vertices_noalloc",
 ]
 
 
@@ -130,6 +131,7 @@ def lib():
     L.tcs_solver_opts_default.argtypes = [C.POINTER(SolverOpts)]
     L.tcs_solver_opts_default.restype = None
     L.tcs_nearest_vertices.argtypes = [vp, vp, sz, vp]
+    L.tcs_nearest_vertices_noalloc.argtypes = [vp, vp, sz, vp]
     L.tcs_random_walker.argtypes = [vp, vp, ci, C.POINTER(SolverOpts), vp, C.POINTER(SolveInfo)]
     L.tcs_segment_cloud.argtypes = [vp, cf, ci, ci, vp, vp, sz, C.POINTER(SolverOpts), vp, vp, C.POINTER(SolveInfo), PP]
     L.tcs_segment_batch.argtypes = [vp, C.POINTER(Scene), ci, cf, ci, ci, C.POINTER(SolverOpts), C.POINTER(SolveInfo)]
@@ -378,6 +380,13 @@ class Graph:
         seed_xyz = _f32(seed_xyz)
         out = np.zeros(len(seed_xyz), np.int32)
         self.ctx.check(lib().tcs_nearest_vertices(self.h, _p(seed_xyz), len(seed_xyz), _p(out)))
+        return out
+
+    def nearest_vertices_noalloc(self, seed_xyz):
+        """tcs_nearest_vertices_noalloc: same result from the fixed device scratch (at most NOALLOC_MAX_SEEDS seeds)."""
+        seed_xyz = _f32(seed_xyz)
+        out = np.zeros(len(seed_xyz), np.int32)
+        self.ctx.check(lib().tcs_nearest_vertices_noalloc(self.h, _p(seed_xyz), len(seed_xyz), _p(out)))
         return out
 
     def random_walker(self, colours, ncolours, opts=None, want_potentials=False):

@@ -7,6 +7,8 @@
 #include <cmath>
 #include <algorithm>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace {
@@ -95,6 +97,69 @@ __global__ void k_seed_nn(size_t V, const float* __restrict__ x, const float* __
       if (sb[w] < best || (sb[w] == best && si[w] < bi)) { best = sb[w]; bi = si[w]; }
     out[s] = (int32_t)bi;
   }
+}
+
+// ---- allocation-free variant of the seed look-up (tcs_nearest_vertices_noalloc) ----------------------------------
+// Scratch of the variant: a file-scope device array (every GPU that loads the library holds these 276 KB until exit).
+//   seeds   : 3 floats per seed (staging of the caller's host array)
+//   nearest : 1 int32 per seed (result, copied back to the caller)
+//   part_d / part_i : per (seed, chunk of the vertex range) the smallest distance and its vertex
+// Every slot a call reads is written by that call first, so nothing has to start at zero; the array keeps the last
+// call's contents, and two calls that overlap on the GPU (different streams / contexts) race on it.
+constexpr int kNoallocChunks = 32;
+struct NoallocScratch {
+  float seeds[3 * TCS_NOALLOC_MAX_SEEDS];
+  int32_t nearest[TCS_NOALLOC_MAX_SEEDS];
+  float part_d[TCS_NOALLOC_MAX_SEEDS * kNoallocChunks];
+  uint32_t part_i[TCS_NOALLOC_MAX_SEEDS * kNoallocChunks];
+};
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoallocScratch)];
+
+// grid (chunks, seeds): block (c, s) scans chunk c of the vertices for seed s; same distance arithmetic and tie rule
+// (lowest vertex id) as k_seed_nn, so the two-stage result is identical to the one-block-per-seed kernel's
+__global__ void __launch_bounds__(256) k_seed_nn_partial(size_t V, const float* __restrict__ x, const float* __restrict__ y,
+                                                         const float* __restrict__ z, const float* __restrict__ seeds,
+                                                         float* __restrict__ part_d, uint32_t* __restrict__ part_i) {
+  const int s = blockIdx.y, c = blockIdx.x, chunks = gridDim.x;
+  const size_t per = (V + chunks - 1) / chunks;
+  const size_t v0 = (size_t)c * per, v1 = v0 + per < V ? v0 + per : V;
+  const float sx = seeds[3 * s], sy = seeds[3 * s + 1], sz = seeds[3 * s + 2];
+  float best = __int_as_float(0x7F800000);
+  uint32_t bi = 0xFFFFFFFFu;
+  for (size_t v = v0 + threadIdx.x; v < v1; v += blockDim.x) {
+    float dx = sx - x[v], dy = sy - y[v], dz = sz - z[v];
+    float d = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
+    if (d < best) { best = d; bi = (uint32_t)v; }
+  }
+  __shared__ float sb[8];
+  __shared__ uint32_t si[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+    uint32_t oi = __shfl_xor_sync(0xFFFFFFFFu, bi, o);
+    if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+  }
+  if ((threadIdx.x & 31) == 0) { sb[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w)
+      if (sb[w] < best || (sb[w] == best && si[w] < bi)) { best = sb[w]; bi = si[w]; }
+    part_d[(size_t)s * chunks + c] = best;   // written for every (seed, chunk), empty chunks included
+    part_i[(size_t)s * chunks + c] = bi;
+  }
+}
+__global__ void k_seed_nn_final(int ns, int chunks, const float* __restrict__ part_d, const uint32_t* __restrict__ part_i,
+                                int32_t* __restrict__ out) {
+  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= ns) return;
+  float best = __int_as_float(0x7F800000);
+  uint32_t bi = 0xFFFFFFFFu;
+  for (int c = 0; c < chunks; ++c) {
+    const float d = part_d[(size_t)s * chunks + c];
+    const uint32_t i = part_i[(size_t)s * chunks + c];
+    if (d < best || (d == best && i < bi)) { best = d; bi = i; }
+  }
+  out[s] = (int32_t)bi;
 }
 
 // colours[nearest[s]] = colour[s] in seed order: later seeds overwrite (impl/random_walker_segmentation.hpp:151-152)
@@ -213,6 +278,48 @@ extern "C" int tcs_nearest_vertices(tcs_graph* g, const float* seed_xyz, size_t 
   DBuf<int32_t> d;
   TRY(tcs_impl_nearest_vertices(g, seed_xyz, ns, d));
   if (ns) CK(cudaMemcpyAsync(out, d.p, 4 * ns, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return TCS_OK;
+}
+
+// Device address of the scratch array, resolved once per device with that device current (in host code the array's
+// name is only a stand-in for the symbol, not an address a kernel could use).
+static int noalloc_scratch_ptr(tcs_ctx* ctx, NoallocScratch** out) {
+  static std::mutex mu;
+  static NoallocScratch* ptrs[64] = {};
+  if (ctx->device < 0 || ctx->device >= 64) return tcs_fail(ctx, TCS_ERR_INPUT, "device index %d outside 0..63", ctx->device);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[ctx->device]) {
+    void* p = nullptr;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) return tcs_fail(ctx, TCS_ERR_CUDA, "cudaGetSymbolAddress returned a null scratch address");
+    ptrs[ctx->device] = (NoallocScratch*)p;
+  }
+  *out = ptrs[ctx->device];
+  return TCS_OK;
+}
+
+extern "C" int tcs_nearest_vertices_noalloc(tcs_graph* g, const float* seed_xyz, size_t ns, int32_t* out) {
+  if (!g || (ns && (!seed_xyz || !out))) return TCS_ERR_INPUT;
+  tcs_ctx* ctx = g->ctx;
+  if (ns > (size_t)TCS_NOALLOC_MAX_SEEDS)
+    return tcs_fail(ctx, TCS_ERR_INPUT, "tcs_nearest_vertices_noalloc: %zu seeds exceed the fixed scratch of TCS_NOALLOC_MAX_SEEDS = %d "
+                    "(use tcs_nearest_vertices)", ns, TCS_NOALLOC_MAX_SEEDS);
+  CK(cudaSetDevice(ctx->device));
+  NoallocScratch* sc = nullptr;
+  TRY(noalloc_scratch_ptr(ctx, &sc));   // ns = 0: set-up only (resolves the address; call once outside a capture)
+  if (ns == 0) return TCS_OK;
+  if (g->V == 0) {
+    for (size_t i = 0; i < ns; ++i) out[i] = -1;
+    return TCS_OK;
+  }
+  CK(cudaMemcpyAsync(sc->seeds, seed_xyz, 12 * ns, cudaMemcpyHostToDevice, ctx->stream));
+  LAUNCH(ctx, k_seed_nn_partial, dim3(kNoallocChunks, (unsigned)ns), 256, 0, g->V, g->x.p, g->y.p, g->z.p, sc->seeds,
+         sc->part_d, sc->part_i);
+  LAUNCH(ctx, k_seed_nn_final, div_up(ns, 128), 128, 0, (int)ns, kNoallocChunks, sc->part_d, sc->part_i, sc->nearest);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(out, sc->nearest, 4 * ns, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   return TCS_OK;
 }
