@@ -197,6 +197,8 @@ typedef struct tcs_scene {
   const float* xyz; size_t xyz_stride;         /* in: as tcs_cloud_upload */
   const uint32_t* rgba; size_t rgba_stride;    /* in: NULL for uncoloured clouds */
   size_t n;
+  const void* d_xyzc; int d_has_color;         /* in: alternative to xyz / rgba - the cloud already on the device as n
+                                                  records {x, y, z, rgba bits} of 16 bytes (borrowed); used when non-NULL */
   const float* seed_xyz; const uint32_t* seed_label; size_t ns;   /* in: setSeeds */
   int32_t* point_cluster;                      /* out: n int32 (may be NULL) */
   uint32_t* vertex_colour;                     /* out: capacity n >= V uint32 (may be NULL) */

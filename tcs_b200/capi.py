@@ -70,7 +70,7 @@ class SolveInfo(C.Structure):
 class Scene(C.Structure):
     """tcs_scene: one cloud + seeds of a batch (tcs_segment_batch)."""
     _fields_ = [("xyz", C.c_void_p), ("xyz_stride", C.c_size_t), ("rgba", C.c_void_p), ("rgba_stride", C.c_size_t),
-                ("n", C.c_size_t), ("seed_xyz", C.c_void_p), ("seed_label", C.c_void_p), ("ns", C.c_size_t),
+                ("n", C.c_size_t), ("d_xyzc", C.c_void_p), ("d_has_color", C.c_int), ("seed_xyz", C.c_void_p), ("seed_label", C.c_void_p), ("ns", C.c_size_t),
                 ("point_cluster", C.c_void_p), ("vertex_colour", C.c_void_p), ("V", C.c_size_t), ("E", C.c_size_t),
                 ("ncolours", C.c_int), ("status", C.c_int)]
 

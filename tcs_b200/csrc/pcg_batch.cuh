@@ -230,10 +230,21 @@ int pcg_solve_batched(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts&
   const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
   DBuf<double> seg_rr;
   TRY(seg_rr.alloc(ctx, (size_t)count));
+  // sampled SpMM timing (bench.py's roofline): one event pair around each of the first launches
+  const int kMaxSamples = 32;
+  std::vector<cudaEvent_t> evs;
+  int samples = 0;
+  if (opts.time_spmm) {
+    evs.resize(2 * kMaxSamples);
+    for (auto& e : evs) CK(cudaEventCreate(&e));
+  }
   while (!converged && it < opts.max_iterations) {
     const int chunk = std::min(probe, opts.max_iterations - it);
     for (int j = 0; j < chunk; ++j, ++it) {
+      const bool timed = opts.time_spmm && samples < kMaxSamples;
+      if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
       launch_spmm(ctx, S, P4, AP4, d_dummy);
+      if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
       ++spmm_launches;
       LAUNCH(ctx, batch::k_dot, grid, 256, dsm, Q, Kp, d_rb.p, (const float4*)P4, (const float4*)AP4, d_pAp);
       LAUNCH(ctx, batch::k_alpha, div_up(count, 128), 128, 0, count, d_rz[cur], d_pAp, d_rz0, frozen.p, done_factor, d_al,
@@ -282,6 +293,17 @@ int pcg_solve_batched(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts&
   }
   S.X.swap(X);
   S.R.release(); S.AP.release();
+  if (samples) {
+    CK(cudaStreamSynchronize(ctx->stream));
+    float sum = 0.f;
+    for (int i = 0; i < samples; ++i) {
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, evs[2 * i], evs[2 * i + 1]));
+      sum += ms;
+    }
+    res.spmm_ms = sum / samples * spmm_launches;
+  }
+  for (auto& e : evs) cudaEventDestroy(e);
   res.iterations = it;
   res.converged = converged;
   res.spmm_launches = spmm_launches;

@@ -202,7 +202,8 @@ extern "C" int tcs_segment_batch(tcs_ctx* ctx, tcs_scene* scenes, int nscenes, f
     if (sc.ns && (!sc.seed_xyz || !sc.seed_label)) return tcs_fail(ctx, TCS_ERR_INPUT, "scene %d: seed arrays missing", s);
     std::vector<uint32_t> seed_colour;
     TRY(seed_colours(ctx, sc.seed_label, sc.ns, seed_colour, &K[s]));
-    TRY(tcs_cloud_upload(ctx, sc.xyz, sc.xyz_stride, sc.rgba, sc.rgba_stride, sc.n));
+    if (sc.d_xyzc) TRY(tcs_cloud_set_device(ctx, sc.d_xyzc, sc.n, sc.d_has_color));
+    else TRY(tcs_cloud_upload(ctx, sc.xyz, sc.xyz_stride, sc.rgba, sc.rgba_stride, sc.n));
     int st = prepare_scene(ctx, resolution, preset, mode, sc.seed_xyz, seed_colour, sc.ns, nullptr, &graphs.g[s]);
     if (st != TCS_OK) return st;
     tcs_graph* g = graphs.g[s];

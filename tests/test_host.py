@@ -187,7 +187,14 @@ def test_bench_reference_arm_prints_its_line():
     assert r.returncode == 0, r.stderr[-2000:]
     line = json.loads(r.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["metric"] == "rw_segmentation_vertices_per_s" and line["value"] > 0
-    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] == 1
+    # the reference is single-threaded per scene: the arm uses the host cores scene-parallel and says how many
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert "worker processes" in line["cpu_baseline"]["sample"]
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--config", "c5", "--cpu-procs", "2",
+                        "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    c5 = json.loads(r.stdout.strip().splitlines()[-1])
+    assert c5["impl"] == "reference" and c5["cpu_baseline"]["cores"] == 2 and c5["config"]["workload"].startswith("C5")
     assert line["e2e"] == {"value": line["value"], "unit": "vertices/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     env = dict(os.environ, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
     r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--small",
