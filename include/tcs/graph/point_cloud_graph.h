@@ -13,14 +13,53 @@
 
 #include "../../tcs_b200.h"
 #include "../pcl_compat.h"
+#include "graph_iterators.h"
 
 namespace boost {
 #ifndef BOOST_GRAPH_PROPERTIES_HPP
-// property tags the reference's call sites name (boost/graph/properties.hpp); defined here only without Boost.Graph
+// The Boost.Graph names the reference's call sites spell out (boost/graph/properties.hpp, graph_traits.hpp,
+// property_map.hpp, tuple.hpp); defined here only when Boost.Graph is not installed.
+#define TCS_BOOST_COMPAT 1
 enum vertex_color_t { vertex_color };
 enum edge_weight_t { edge_weight };
 enum vertex_index_t { vertex_index };
 enum edge_index_t { edge_index };
+struct undirected_tag {};
+struct allow_parallel_edge_tag {};
+struct vertex_list_graph_tag {};
+// boost::graph_traits<G>: reads the graph's own typedefs
+template <typename G>
+struct graph_traits {
+  typedef typename G::vertex_descriptor vertex_descriptor;
+  typedef typename G::edge_descriptor edge_descriptor;
+  typedef typename G::vertex_iterator vertex_iterator;
+  typedef typename G::edge_iterator edge_iterator;
+  typedef typename G::out_edge_iterator out_edge_iterator;
+  typedef typename G::in_edge_iterator in_edge_iterator;
+  typedef typename G::adjacency_iterator adjacency_iterator;
+  typedef typename G::vertices_size_type vertices_size_type;
+  typedef typename G::edges_size_type edges_size_type;
+  typedef typename G::degree_size_type degree_size_type;
+  typedef typename G::directed_category directed_category;
+  typedef typename G::edge_parallel_category edge_parallel_category;
+  typedef typename G::traversal_category traversal_category;
+  static vertex_descriptor null_vertex() { return (vertex_descriptor)-1; }
+};
+// boost::property_traits<Map>
+template <typename Map>
+struct property_traits {
+  typedef typename Map::value_type value_type;
+  typedef typename Map::reference reference;
+  typedef typename Map::key_type key_type;
+};
+// boost::tie (a, b) = pair
+template <typename A, typename B>
+struct tcs_tied {
+  A& a; B& b;
+  tcs_tied(A& a_, B& b_) : a(a_), b(b_) {}
+  template <typename U, typename V> tcs_tied& operator=(const std::pair<U, V>& p) { a = p.first; b = p.second; return *this; }
+};
+template <typename A, typename B> inline tcs_tied<A, B> tie(A& a, B& b) { return tcs_tied<A, B>(a, b); }
 #endif
 }  // namespace boost
 
@@ -83,12 +122,23 @@ class point_cloud_graph {
   typedef typename point_cloud_type::Ptr point_cloud_ptr;
   typedef typename point_cloud_type::ConstPtr point_cloud_const_ptr;
   typedef uint32_t vertex_descriptor;
-  struct edge_descriptor {
-    uint32_t src, tgt, idx;
-    bool operator==(const edge_descriptor& o) const { return idx == o.idx; }
-  };
+  typedef tcs::detail::edge_descriptor edge_descriptor;
   typedef size_t vertices_size_type;
   typedef size_t edges_size_type;
+  typedef size_t degree_size_type;
+  // what boost::graph_traits reads (VertexListGraph, EdgeListGraph, IncidenceGraph, AdjacencyGraph; undirected, vecS)
+  typedef tcs::detail::vertex_iterator vertex_iterator;
+  typedef tcs::detail::edge_iterator<point_cloud_graph> edge_iterator;
+  typedef tcs::detail::out_edge_iterator<point_cloud_graph> out_edge_iterator;
+  typedef out_edge_iterator in_edge_iterator;
+  typedef tcs::detail::adjacency_iterator<point_cloud_graph> adjacency_iterator;
+  typedef boost::undirected_tag directed_category;
+  typedef boost::allow_parallel_edge_tag edge_parallel_category;
+  typedef boost::vertex_list_graph_tag traversal_category;
+  typedef tcs::detail::edge_weight_map<point_cloud_graph> edge_weight_map;
+  typedef tcs::detail::const_edge_weight_map<point_cloud_graph> const_edge_weight_map;
+  typedef tcs::detail::vertex_color_map<point_cloud_graph> vertex_color_map;
+  typedef tcs::detail::const_vertex_color_map<point_cloud_graph> const_vertex_color_map;
   typedef std::integral_constant<bool, tcs::has_color<PointT>::value> colored;
 
   point_cloud_graph() : cloud_(new point_cloud_type) {}
@@ -262,32 +312,137 @@ class point_cloud_graph {
   bool bundle_host_dirty_ = false, topo_host_dirty_ = false, weight_host_dirty_ = false, colour_host_dirty_ = false;
 };
 
-// ---- BGL-style free functions (the subset the reference's call sites use) --------------------------------------
+// ---- BGL free functions (VertexListGraph / EdgeListGraph / IncidenceGraph / AdjacencyGraph / PropertyGraph) --------
+// Same names and meaning as for the reference's type (include/graph/point_cloud_graph.h:590-835); iterator pairs work
+// with boost::tie and the reference's as_range (include/as_range.h).
 template <typename P> inline size_t num_vertices(const point_cloud_graph<P>& g) { return g.num_vertices(); }
 template <typename P> inline size_t num_edges(const point_cloud_graph<P>& g) { return g.num_edges(); }
 template <typename P>
 inline std::pair<typename point_cloud_graph<P>::edge_descriptor, bool> add_edge(uint32_t u, uint32_t v, point_cloud_graph<P>& g) {
   return g.add_edge(u, v);
 }
-template <typename P> inline uint32_t source(const typename point_cloud_graph<P>::edge_descriptor& e, const point_cloud_graph<P>&) { return e.src; }
-template <typename P> inline uint32_t target(const typename point_cloud_graph<P>::edge_descriptor& e, const point_cloud_graph<P>&) { return e.tgt; }
+template <typename P> inline uint32_t source(const tcs::detail::edge_descriptor& e, const point_cloud_graph<P>&) { return e.src; }
+template <typename P> inline uint32_t target(const tcs::detail::edge_descriptor& e, const point_cloud_graph<P>&) { return e.tgt; }
+template <typename P>
+inline std::pair<tcs::detail::vertex_iterator, tcs::detail::vertex_iterator> vertices(const point_cloud_graph<P>& g) {
+  return std::make_pair(tcs::detail::vertex_iterator(0), tcs::detail::vertex_iterator((uint32_t)g.num_vertices()));
+}
+template <typename P>
+inline std::pair<typename point_cloud_graph<P>::edge_iterator, typename point_cloud_graph<P>::edge_iterator> edges(
+    const point_cloud_graph<P>& g) {
+  typedef typename point_cloud_graph<P>::edge_iterator It;
+  return std::make_pair(It(&g, 0), It(&g, g.edge_sources().size()));
+}
+template <typename P>
+inline std::pair<typename point_cloud_graph<P>::out_edge_iterator, typename point_cloud_graph<P>::out_edge_iterator> out_edges(
+    uint32_t v, const point_cloud_graph<P>& g) {
+  typedef typename point_cloud_graph<P>::out_edge_iterator It;
+  const std::vector<uint32_t>& rp = g.out_rowptr();
+  return std::make_pair(It(&g, v, rp[v]), It(&g, v, rp[v + 1]));
+}
+// undirected: the in-edges of a vertex are its out-edges
+template <typename P>
+inline std::pair<typename point_cloud_graph<P>::out_edge_iterator, typename point_cloud_graph<P>::out_edge_iterator> in_edges(
+    uint32_t v, const point_cloud_graph<P>& g) {
+  return out_edges(v, g);
+}
+template <typename P>
+inline std::pair<typename point_cloud_graph<P>::adjacency_iterator, typename point_cloud_graph<P>::adjacency_iterator>
+adjacent_vertices(uint32_t v, const point_cloud_graph<P>& g) {
+  typedef typename point_cloud_graph<P>::adjacency_iterator It;
+  const std::vector<uint32_t>& rp = g.out_rowptr();
+  return std::make_pair(It(&g, rp[v]), It(&g, rp[v + 1]));
+}
+template <typename P> inline size_t out_degree(uint32_t v, const point_cloud_graph<P>& g) { return g.out_rowptr()[v + 1] - g.out_rowptr()[v]; }
+template <typename P> inline size_t in_degree(uint32_t v, const point_cloud_graph<P>& g) { return out_degree(v, g); }
+template <typename P> inline size_t degree(uint32_t v, const point_cloud_graph<P>& g) { return out_degree(v, g); }
+// boost::edge (u, v, g): the first edge between u and v in u's out-edge order
+template <typename P>
+inline std::pair<typename point_cloud_graph<P>::edge_descriptor, bool> edge(uint32_t u, uint32_t v, const point_cloud_graph<P>& g) {
+  const std::vector<uint32_t>& rp = g.out_rowptr();
+  for (uint32_t a = rp[u]; a < rp[u + 1]; ++a)
+    if (g.out_targets()[a] == v) {
+      const uint32_t id = g.out_edge_ids()[a];
+      typename point_cloud_graph<P>::edge_descriptor e = {g.edge_sources()[id], g.edge_targets()[id], id};
+      return std::make_pair(e, true);
+    }
+  typename point_cloud_graph<P>::edge_descriptor none = {0u, 0u, 0xFFFFFFFFu};
+  return std::make_pair(none, false);
+}
 // edge i of the global edge list (insertion order = edge id)
 template <typename P> inline typename point_cloud_graph<P>::edge_descriptor edge_at(size_t i, const point_cloud_graph<P>& g) {
   typename point_cloud_graph<P>::edge_descriptor e = {g.edge_sources()[i], g.edge_targets()[i], (uint32_t)i};
   return e;
 }
-// adjacent vertices of v in out-edge (insertion) order
-template <typename P> inline std::vector<uint32_t> adjacent_vertices(uint32_t v, const point_cloud_graph<P>& g) {
-  const std::vector<uint32_t>& rp = g.out_rowptr();
-  return std::vector<uint32_t>(g.out_targets().begin() + rp[v], g.out_targets().begin() + rp[v + 1]);
-}
-template <typename P> inline size_t out_degree(uint32_t v, const point_cloud_graph<P>& g) { return g.out_rowptr()[v + 1] - g.out_rowptr()[v]; }
 template <typename P> inline typename pcl::PointCloud<P>::ConstPtr point_cloud(const point_cloud_graph<P>& g) { return g.point_cloud(); }
-// property maps: get(boost::vertex_color, g)[v], get(boost::edge_weight, g)[e.idx]
-template <typename P> inline std::vector<uint32_t>& get(boost::vertex_color_t, point_cloud_graph<P>& g) { return g.vertex_colors(); }
-template <typename P> inline const std::vector<uint32_t>& get(boost::vertex_color_t, const point_cloud_graph<P>& g) { return g.vertex_colors(); }
-template <typename P> inline std::vector<float>& get(boost::edge_weight_t, point_cloud_graph<P>& g) { return g.edge_weights(); }
-template <typename P> inline const std::vector<float>& get(boost::edge_weight_t, const point_cloud_graph<P>& g) { return g.edge_weights(); }
+// property maps: get (boost::vertex_color, g)[v], get (boost::edge_weight, g)[e]  (also [edge id])
+template <typename P> inline typename point_cloud_graph<P>::vertex_color_map get(boost::vertex_color_t, point_cloud_graph<P>& g) {
+  return typename point_cloud_graph<P>::vertex_color_map(&g);
+}
+template <typename P> inline typename point_cloud_graph<P>::const_vertex_color_map get(boost::vertex_color_t, const point_cloud_graph<P>& g) {
+  return typename point_cloud_graph<P>::const_vertex_color_map(&g);
+}
+template <typename P> inline typename point_cloud_graph<P>::edge_weight_map get(boost::edge_weight_t, point_cloud_graph<P>& g) {
+  return typename point_cloud_graph<P>::edge_weight_map(&g);
+}
+template <typename P> inline typename point_cloud_graph<P>::const_edge_weight_map get(boost::edge_weight_t, const point_cloud_graph<P>& g) {
+  return typename point_cloud_graph<P>::const_edge_weight_map(&g);
+}
+template <typename P> inline tcs::detail::edge_index_map<point_cloud_graph<P>> get(boost::edge_index_t, const point_cloud_graph<P>&) {
+  return tcs::detail::edge_index_map<point_cloud_graph<P>>();
+}
+template <typename P> inline tcs::detail::vertex_index_map get(boost::vertex_index_t, const point_cloud_graph<P>&) {
+  return tcs::detail::vertex_index_map();
+}
+// get (tag, g, key) / put (tag, g, key, value)
+template <typename Tag, typename P, typename Key>
+inline auto get(Tag tag, const point_cloud_graph<P>& g, const Key& k) -> typename std::decay<decltype(get(tag, g)[k])>::type {
+  return get(tag, g)[k];
+}
+template <typename Tag, typename P, typename Key, typename Value>
+inline void put(Tag tag, point_cloud_graph<P>& g, const Key& k, const Value& v) { get(tag, g)[k] = v; }
 
 }  // namespace graph
 }  // namespace pcl
+
+// get (map, key) / put (map, key, value) on the maps above (boost/property_map/property_map.hpp spelling)
+namespace tcs {
+namespace detail {
+template <typename G> inline float& get(const edge_weight_map<G>& m, const edge_descriptor& e) { return m[e]; }
+template <typename G> inline const float& get(const const_edge_weight_map<G>& m, const edge_descriptor& e) { return m[e]; }
+template <typename G> inline uint32_t& get(const vertex_color_map<G>& m, uint32_t v) { return m[v]; }
+template <typename G> inline const uint32_t& get(const const_vertex_color_map<G>& m, uint32_t v) { return m[v]; }
+template <typename G> inline void put(const edge_weight_map<G>& m, const edge_descriptor& e, float w) { m[e] = w; }
+template <typename G> inline void put(const vertex_color_map<G>& m, uint32_t v, uint32_t c) { m[v] = c; }
+}  // namespace detail
+}  // namespace tcs
+
+// The reference's call sites qualify these with boost:: (boost::edges (graph), boost::source (edge, graph), ...).
+namespace boost {
+using pcl::graph::num_vertices;
+using pcl::graph::num_edges;
+using pcl::graph::add_edge;
+using pcl::graph::source;
+using pcl::graph::target;
+using pcl::graph::vertices;
+using pcl::graph::edges;
+using pcl::graph::out_edges;
+using pcl::graph::in_edges;
+using pcl::graph::adjacent_vertices;
+using pcl::graph::out_degree;
+using pcl::graph::in_degree;
+using pcl::graph::degree;
+using pcl::graph::edge;
+using pcl::graph::get;
+using pcl::graph::put;
+using tcs::detail::get;
+using tcs::detail::put;
+#ifdef TCS_BOOST_COMPAT
+// boost::property_map<Graph, Tag>::type
+template <typename G, typename Tag> struct property_map;
+template <typename G> struct property_map<G, edge_weight_t> { typedef typename G::edge_weight_map type; typedef typename G::const_edge_weight_map const_type; };
+template <typename G> struct property_map<G, vertex_color_t> { typedef typename G::vertex_color_map type; typedef typename G::const_vertex_color_map const_type; };
+template <typename G> struct property_map<G, edge_index_t> { typedef tcs::detail::edge_index_map<G> type; typedef type const_type; };
+template <typename G> struct property_map<G, vertex_index_t> { typedef tcs::detail::vertex_index_map type; typedef type const_type; };
+#endif
+}  // namespace boost

@@ -100,7 +100,9 @@ class RandomWalkerSegmentation : public pcl::PCLBase<PointT> {
       for (size_t i = 0; i < ns; ++i) { sxyz[3 * i] = seeds_->at(i).x; sxyz[3 * i + 1] = seeds_->at(i).y; sxyz[3 * i + 2] = seeds_->at(i).z; }
       std::vector<int32_t> nearest(ns);
       graph_->ctx().check(tcs_nearest_vertices(graph_->device(), sxyz.data(), ns, nearest.data()));
-      for (size_t i = 0; i < ns; ++i) colors[nearest[i]] = label_color_[seeds_->at(i).label];
+      // a seed with NaN / Inf coordinates has no nearest vertex (-1): it paints nothing, like k_paint_seeds in the C ABI
+      for (size_t i = 0; i < ns; ++i)
+        if (nearest[i] >= 0 && (size_t)nearest[i] < V) colors[nearest[i]] = label_color_[seeds_->at(i).label];
     }
     tcs_solver_opts opts = solver_opts_;
     bool ok = true;

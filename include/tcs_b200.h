@@ -153,6 +153,14 @@ int tcs_smoothen(tcs_graph* g, float spatial_sigma, float influence_sigma);
 int tcs_signed_curvatures(tcs_graph* g);
 /* EdgeWeightComputer::compute, graph/impl/edge_weight_computer.hpp:110-188 */
 int tcs_edge_weights(tcs_graph* g, const tcs_term* terms, int nterms, float threshold, int policy, int mode);
+/* EdgeWeightComputer::setTermBalancingFunction (graph/edge_weight_computer.h:207,325) + compute: the function that turns
+ * a (normalised) term distance d and the term's influence s into a factor of the edge weight.  The reference accepts
+ * any boost::function<float (float, float)>; the device offers this closed set (all are 1 for s <= 0, like the
+ * reference's default):  GAUSSIAN exp(-d/s) (the default, edge_weight_computer.h:333-337) | INVERSE 1/(1 + d/s) |
+ * GAUSSIAN_SQUARED exp(-(d/s)^2) | LINEAR max(0, 1 - d/s). */
+enum { TCS_BALANCE_GAUSSIAN = 0, TCS_BALANCE_INVERSE = 1, TCS_BALANCE_GAUSSIAN_SQUARED = 2, TCS_BALANCE_LINEAR = 3 };
+int tcs_edge_weights_ex(tcs_graph* g, const tcs_term* terms, int nterms, float threshold, int policy, int mode,
+                        int balancing);
 /* createSubgraphsFromConnectedComponents, graph/impl/common.hpp:134-149: component id per vertex, ids in
  * order of the smallest member vertex.  component (host, V ints) may be NULL. */
 int tcs_components(tcs_graph* g, int* ncomponents, int32_t* component);

@@ -84,7 +84,9 @@ void orc_normals(orc_graph* g, int one_ring, int mode);               /* graph/i
 void orc_smoothen(orc_graph* g, float spatial_sigma, float influence_sigma); /* common.hpp:241-279 */
 void orc_signed_curvatures(orc_graph* g);                             /* common.hpp:105-132 */
 int orc_edge_weights(orc_graph* g, const orc_term* terms, int nterms, float threshold, int policy,
-                     int mode);                                       /* edge_weight_computer.hpp:110-188 */
+                     int mode);
+/* the same with EdgeWeightComputer::setTermBalancingFunction: 0 Gaussian (default), 1 inverse, 2 squared Gaussian, 3 linear */
+int orc_edge_weights_ex(orc_graph* g, const orc_term* terms, int nterms, float threshold, int policy, int mode, int balancing);                                       /* edge_weight_computer.hpp:110-188 */
 int orc_components(const orc_graph* g, int32_t* component);           /* common.hpp:134-149 */
 
 /* ---- random walker --------------------------------------------------------------------------------- */

@@ -232,12 +232,28 @@ float term_distance(const orc_graph* g, int kind, uint32_t a, uint32_t b) {
 
 // EdgeWeightComputer::gaussian (edge_weight_computer.h:333-337)
 inline float gaussian(float val, float influence) { return influence > 0.0f ? orc_expf(-val / influence) : 1.0f; }
+// setTermBalancingFunction (edge_weight_computer.h:207,325): the closed set the device implements (ORC_BALANCE_*);
+// 0 = the reference's default Gaussian
+inline float balance(int kind, float val, float influence) {
+  if (kind == 0) return gaussian(val, influence);
+  if (!(influence > 0.0f)) return 1.0f;
+  const float q = val / influence;
+  if (kind == 1) return 1.0f / (1.0f + q);
+  if (kind == 2) return orc_expf(-(q * q));
+  const float l = 1.0f - q;
+  return l > 0.0f ? l : 0.0f;
+}
 
 }  // namespace
 
 // graph/impl/edge_weight_computer.hpp:110-188
 extern "C" int orc_edge_weights(orc_graph* g, const orc_term* terms, int nterms, float threshold, int policy,
                                 int mode) {
+  return orc_edge_weights_ex(g, terms, nterms, threshold, policy, mode, 0);
+}
+
+extern "C" int orc_edge_weights_ex(orc_graph* g, const orc_term* terms, int nterms, float threshold, int policy,
+                                   int mode, int balancing) {
   const size_t E = g->E, V = g->V;
   // terms are stored per normalisation class and evaluated plain -> global -> local (:148-154)
   std::vector<int> plain, glob, loc;
@@ -285,13 +301,13 @@ extern "C" int orc_edge_weights(orc_graph* g, const orc_term* terms, int nterms,
     bool convex = g->curv[v1] > 0.0f && g->curv[v2] > 0.0f;  // detail::IsConvex (:95-102)
     float a = 1.0f;
     auto influence = [&](int t, bool cvx) { return terms[t].influence * (cvx ? terms[t].convex_mult : 1.0f); };
-    for (int t : plain) a *= gaussian(term_distance(g, terms[t].kind, v1, v2), influence(t, convex));
-    for (size_t i = 0; i < glob.size(); ++i) a *= gaussian(gd[i][e] / gavg[i], influence(glob[i], convex));
+    for (int t : plain) a *= balance(balancing, term_distance(g, terms[t].kind, v1, v2), influence(t, convex));
+    for (size_t i = 0; i < glob.size(); ++i) a *= balance(balancing, gd[i][e] / gavg[i], influence(glob[i], convex));
     for (size_t i = 0; i < loc.size(); ++i) {
       // LocallyNormalizedTerm::round2 (edge_weight_computer.h:451-460)
       float n = (lsum[i][v1] + lsum[i][v2]) / 2.0f;
       float w = (n > 0.0f && influence(loc[i], false) > 0.0f) ? ld[i][e] / n : 0.0f;
-      a *= gaussian(w, influence(loc[i], convex));
+      a *= balance(balancing, w, influence(loc[i], convex));
     }
     g->ew[e] = a;
   }

@@ -18,6 +18,7 @@ NORM_NONE, NORM_GLOBAL, NORM_LOCAL = 0, 1, 2
 SMALL_IGNORE, SMALL_COERCE, SMALL_REMOVE = 0, 1, 2
 MODE_PARITY, MODE_FAST = 0, 1
 PRESET_CLASS, PRESET_CLI = 0, 1
+BALANCE_GAUSSIAN, BALANCE_INVERSE, BALANCE_GAUSSIAN_SQUARED, BALANCE_LINEAR = 0, 1, 2, 3
 OK, ERR_CUDA, ERR_INPUT, ERR_DEPTH, ERR_NOT_CONVERGED, ERR_STATE = 0, -1, -2, -3, -4, -5
 MAX_LABELS = 64
 NOALLOC_MAX_SEEDS = 1024
@@ -39,7 +40,7 @@ EXPORTS = [
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
     "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm", "tcs_graph_download_best",
-    "tcs_build_nn_graph", "tcs_segment_batch", "tcs_nearest_vertices_noalloc",
+    "tcs_build_nn_graph", "tcs_segment_batch", "tcs_nearest_vertices_noalloc", "tcs_edge_weights_ex",
 ]
 
 
@@ -127,6 +128,7 @@ def lib():
     L.tcs_smoothen.argtypes = [vp, cf, cf]
     L.tcs_signed_curvatures.argtypes = [vp]
     L.tcs_edge_weights.argtypes = [vp, vp, ci, cf, ci, ci]
+    L.tcs_edge_weights_ex.argtypes = [vp, vp, ci, cf, ci, ci, ci]
     L.tcs_components.argtypes = [vp, C.POINTER(ci), vp]
     L.tcs_solver_opts_default.argtypes = [C.POINTER(SolverOpts)]
     L.tcs_solver_opts_default.restype = None
@@ -366,9 +368,9 @@ class Graph:
     def signed_curvatures(self):
         self.ctx.check(lib().tcs_signed_curvatures(self.h))
 
-    def edge_weights(self, terms=TERMS_CLASS, threshold=1e-5, policy=SMALL_COERCE, mode=MODE_PARITY):
+    def edge_weights(self, terms=TERMS_CLASS, threshold=1e-5, policy=SMALL_COERCE, mode=MODE_PARITY, balancing=BALANCE_GAUSSIAN):
         arr = (Term * len(terms))(*[Term(*t) for t in terms])
-        self.ctx.check(lib().tcs_edge_weights(self.h, arr, len(terms), threshold, policy, mode))
+        self.ctx.check(lib().tcs_edge_weights_ex(self.h, arr, len(terms), threshold, policy, mode, balancing))
 
     def components(self):
         comp = np.zeros(self.V, np.int32)

@@ -77,13 +77,13 @@ struct Hierarchy {
 };
 
 // ---------------------------------------------------------------------------------------------------- set-up kernels
-__global__ void k_excess(int n, const uint32_t* __restrict__ rowptr, const float* __restrict__ val,
+__global__ void k_excess(int n, int keep_sign, const uint32_t* __restrict__ rowptr, const float* __restrict__ val,
                          const float* __restrict__ diag, double* __restrict__ g) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   double s = (double)diag[i];
   for (uint32_t a = rowptr[i]; a < rowptr[i + 1]; ++a) s += (double)val[a];
-  g[i] = s > 0.0 ? s : 0.0;
+  g[i] = (s > 0.0 || keep_sign) ? s : 0.0;
 }
 
 __global__ void k_fill_u32(size_t n, uint32_t v, uint32_t* __restrict__ p) {
@@ -280,19 +280,32 @@ __global__ void __launch_bounds__(1024) k_dense_invert(int m, const double* __re
   for (int t = threadIdx.x; t < m * m; t += blockDim.x) Einv[t] = sE[t];
 }
 
-// e = E^-1 r on the bottom level (m <= kBottomMax): thread (a, q)
-__global__ void k_dense_apply(int m, int Q, const double* __restrict__ Einv, const float4* __restrict__ r,
-                              float4* __restrict__ e) {
-  int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= m * Q) return;
-  const int a = t / Q, q = t - a * Q;
+// e = E^-1 r on the bottom level (m <= kBottomMax).  One CTA per row a: thread (part, q) sums its share of the b range
+// in float64, the shares are added in a fixed order (deterministic).  (One thread per (a, q) with a serial loop over b
+// took 46 us for m = 126: four CTAs of dependent loads.)
+__global__ void __launch_bounds__(128) k_dense_apply(int m, int Q, const double* __restrict__ Einv, const float4* __restrict__ r,
+                                                     float4* __restrict__ e) {
+  __shared__ double sm[128 * 4];
+  const int a = blockIdx.x;
+  const int parts = blockDim.x / Q;
+  const int part = threadIdx.x / Q, q = threadIdx.x - part * Q;
   double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-  for (int b = 0; b < m; ++b) {
-    const double f = Einv[(size_t)a * m + b];
-    const float4 v = r[(size_t)b * Q + q];
-    s0 += f * v.x; s1 += f * v.y; s2 += f * v.z; s3 += f * v.w;
+  if (part < parts)
+    for (int b = part; b < m; b += parts) {
+      const double f = Einv[(size_t)a * m + b];
+      const float4 v = r[(size_t)b * Q + q];
+      s0 += f * v.x; s1 += f * v.y; s2 += f * v.z; s3 += f * v.w;
+    }
+  sm[threadIdx.x * 4 + 0] = s0; sm[threadIdx.x * 4 + 1] = s1; sm[threadIdx.x * 4 + 2] = s2; sm[threadIdx.x * 4 + 3] = s3;
+  __syncthreads();
+  if (threadIdx.x < Q) {
+    double t0 = 0.0, t1 = 0.0, t2 = 0.0, t3 = 0.0;
+    for (int p = 0; p < parts; ++p) {
+      const double* v = sm + (size_t)(p * Q + q) * 4;
+      t0 += v[0]; t1 += v[1]; t2 += v[2]; t3 += v[3];
+    }
+    e[(size_t)a * Q + q] = make_float4((float)t0, (float)t1, (float)t2, (float)t3);
   }
-  e[t] = make_float4((float)s0, (float)s1, (float)s2, (float)s3);
 }
 
 // ---------------------------------------------------------------------------------------------------- cycle kernels
@@ -495,14 +508,14 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Hierarchy& H) {
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
   CK(cudaEventRecord(e0, ctx->stream));
-  const float w = (float)env_double("TCS_AMG_OMEGA", 0.8);
-  const int rounds = env_i("TCS_AMG_ROUNDS", 4);
+  const float w = (float)env_double("TCS_AMG_OMEGA", 0.9);
+  const int rounds = env_i("TCS_AMG_ROUNDS", 2);
   const int passes = std::max(1, env_i("TCS_AMG_PASSES", 2));
-  H.over = (float)env_double("TCS_AMG_OVER", 1.5);
+  H.over = (float)env_double("TCS_AMG_OVER", 1.3);
   Level& L0 = H.L[0];
   L0.A.n = n; L0.A.nnz = S.nnz_off; L0.A.rowptr = S.rowptr.p; L0.A.col = S.col.p; L0.A.val = S.val.p; L0.A.diag = S.diag.p;
   TRY(L0.g.alloc(ctx, n));
-  LAUNCH(ctx, k_excess, div_up(n, 256), 256, 0, n, S.rowptr.p, S.val.p, S.diag.p, L0.g.p);
+  LAUNCH(ctx, k_excess, div_up(n, 256), 256, 0, n, env_i("TCS_AMG_SIGNED", 0), S.rowptr.p, S.val.p, S.diag.p, L0.g.p);
   int lev = 0;
   while (lev + 1 < kMaxLevels) {
     Level& F = H.L[lev];
@@ -617,7 +630,7 @@ inline int apply(tcs_ctx* ctx, Hierarchy& H, int Q, const float4* R4, double* rz
   {
     Level& B = H.L[last];
     if (H.dense) {
-      LAUNCH(ctx, k_dense_apply, div_up((size_t)H.m * Q, 128), 128, 0, H.m, Q, H.Einv.p, (const float4*)B.r.p, (float4*)B.t.p);
+      LAUNCH(ctx, k_dense_apply, (unsigned)H.m, 128, 0, H.m, Q, H.Einv.p, (const float4*)B.r.p, (float4*)B.t.p);
     } else {
       // no dense inverse (many collapsed components): the smoother is exact on rows without off-diagonal entries
       LAUNCH(ctx, (k_level_spmm<1, 0>), spmm_grid(ctx, B.A.n, Q), 256, dsm, B.A.n, Q, B.A.rowptr, B.A.col, B.A.val, B.gdiag.p,

@@ -1319,7 +1319,7 @@ int tcs_impl_pcg_solve(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts
   const int amg_probe = std::max(1, env_int("TCS_AMG_PROBE", 4));
   const double amg_stage = amg::env_double("TCS_AMG_STAGE", 1e-3);
   const int amg_restart = env_int("TCS_AMG_RESTART", 1);
-  const int amg_x64 = env_int("TCS_AMG_X64", 1);
+  const int amg_x64 = env_int("TCS_AMG_X64", 0);
   std::vector<double> stage_start((size_t)Kp0, 1.0);
   if (AH.on) next_chunk = amg_probe;
   bool replaced = true;    // the last check replaced r: the next step uses the exact line search (it > 0)

@@ -18,6 +18,7 @@ struct TermSet {
   int norm[MAX_TERMS];
   int slot[MAX_TERMS];     // index of the raw-distance array for normalised terms
   int nslots;
+  int balancing;           // TCS_BALANCE_*: how a (normalised) distance becomes a factor of the weight
 };
 
 struct VertexView {
@@ -50,6 +51,18 @@ __device__ float term_distance(const VertexView& g, int kind, uint32_t a, uint32
 // EdgeWeightComputer::gaussian (edge_weight_computer.h:333-337); std::exp(float) := float64 exp rounded once
 __device__ __forceinline__ float gaussian(float val, float influence) {
   return influence > 0.0f ? (float)exp((double)(-val / influence)) : 1.0f;
+}
+// EdgeWeightComputer::setTermBalancingFunction (edge_weight_computer.h:325): the reference takes any
+// boost::function<float (float, float)>; a host callable cannot run here, so the device offers a closed set
+// (TCS_BALANCE_*), the reference's default Gaussian first.  Every function is 1 for influence <= 0 like the default.
+__device__ __forceinline__ float balance(int kind, float val, float influence) {
+  if (kind == TCS_BALANCE_GAUSSIAN) return gaussian(val, influence);
+  if (!(influence > 0.0f)) return 1.0f;
+  const float q = val / influence;
+  if (kind == TCS_BALANCE_INVERSE) return 1.0f / (1.0f + q);
+  if (kind == TCS_BALANCE_GAUSSIAN_SQUARED) return (float)exp((double)(-(q * q)));
+  const float l = 1.0f - q;   // TCS_BALANCE_LINEAR
+  return l > 0.0f ? l : 0.0f;
 }
 
 // round 1: raw distances of the normalised terms, raw[slot * E + e]
@@ -118,14 +131,14 @@ __global__ void k_edge_weight(size_t E, const uint32_t* __restrict__ esrc, const
   for (int t = 0; t < ts.n; ++t) {
     float infl = ts.influence[t] * (convex ? ts.cmult[t] : 1.0f);
     if (ts.norm[t] == TCS_NORM_NONE) {
-      a *= gaussian(term_distance(g, ts.kind[t], v1, v2), infl);
+      a *= balance(ts.balancing, term_distance(g, ts.kind[t], v1, v2), infl);
     } else if (ts.norm[t] == TCS_NORM_GLOBAL) {
-      a *= gaussian(raw[(size_t)ts.slot[t] * E + e] / gavg[ts.slot[t]], infl);
+      a *= balance(ts.balancing, raw[(size_t)ts.slot[t] * E + e] / gavg[ts.slot[t]], infl);
     } else {
       const float* m = lmean + (size_t)ts.slot[t] * V;
       float n = (m[v1] + m[v2]) / 2.0f;
       float w = (n > 0.0f && ts.influence[t] > 0.0f) ? raw[(size_t)ts.slot[t] * E + e] / n : 0.0f;
-      a *= gaussian(w, infl);
+      a *= balance(ts.balancing, w, infl);
     }
   }
   if (coerce && a < threshold) a = threshold;
@@ -151,14 +164,22 @@ __global__ void k_compact_edges(size_t E, const uint32_t* __restrict__ keep, con
 
 extern "C" int tcs_edge_weights(tcs_graph* g, const tcs_term* terms, int nterms, float threshold, int policy,
                                 int mode) {
+  return tcs_edge_weights_ex(g, terms, nterms, threshold, policy, mode, TCS_BALANCE_GAUSSIAN);
+}
+
+extern "C" int tcs_edge_weights_ex(tcs_graph* g, const tcs_term* terms, int nterms, float threshold, int policy,
+                                   int mode, int balancing) {
   if (!g || (nterms && !terms) || nterms < 0) return TCS_ERR_INPUT;
   tcs_ctx* ctx = g->ctx;
+  if (balancing < TCS_BALANCE_GAUSSIAN || balancing > TCS_BALANCE_LINEAR)
+    return tcs_fail(ctx, TCS_ERR_INPUT, "unknown term balancing function %d", balancing);
   if (nterms > MAX_TERMS) return tcs_fail(ctx, TCS_ERR_INPUT, "at most %d edge-weight terms", MAX_TERMS);
   CK(cudaSetDevice(ctx->device));
   const size_t E = g->E, V = g->V;
   if (E == 0) return TCS_OK;
   TermSet ts;
   memset(&ts, 0, sizeof ts);
+  ts.balancing = balancing;
   for (int pass = 0; pass < 3; ++pass)
     for (int i = 0; i < nterms; ++i) {
       if (terms[i].kind < 0 || terms[i].kind > 3 || terms[i].normalization < 0 || terms[i].normalization > 2)

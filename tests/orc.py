@@ -69,6 +69,7 @@ def lib():
         L.orc_smoothen.argtypes = [vp, C.c_float, C.c_float]
         L.orc_signed_curvatures.argtypes = [vp]
         L.orc_edge_weights.argtypes = [vp, vp, C.c_int, C.c_float, C.c_int, C.c_int]
+        L.orc_edge_weights_ex.argtypes = [vp, vp, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
         L.orc_components.argtypes = [vp, vp]
         L.orc_nearest_vertices.argtypes = [vp, vp, sz, vp]
         L.orc_random_walker.argtypes = [vp, vp, C.c_int, C.c_int, vp, vp]
@@ -200,9 +201,9 @@ class Graph:
     def signed_curvatures(self):
         lib().orc_signed_curvatures(self.h)
 
-    def edge_weights(self, terms=PRESET_CLASS, threshold=1e-5, policy=SMALL_COERCE, mode=MODE_PARITY):
+    def edge_weights(self, terms=PRESET_CLASS, threshold=1e-5, policy=SMALL_COERCE, mode=MODE_PARITY, balancing=0):
         arr = (Term * len(terms))(*[Term(*t) for t in terms])
-        return lib().orc_edge_weights(self.h, arr, len(terms), threshold, policy, mode)
+        return lib().orc_edge_weights_ex(self.h, arr, len(terms), threshold, policy, mode, balancing)
 
     def components(self):
         comp = np.zeros(self.V, np.int32)

@@ -106,3 +106,24 @@ def test_graph_io_round_trip_of_a_device_graph(tmp_path):
     _build()
     r = subprocess.run([GIO, str(tmp_path), "device"], capture_output=True, text=True)
     assert r.returncode == 0 and "graph_io_check ok" in r.stdout, r.stdout + r.stderr
+
+
+REFCALL = os.path.join(ROOT, "tcs_b200", "cpp", "ref_caller_check")
+
+
+def test_reference_caller_code_compiles():
+    """tests/cpp/ref_caller_check.cpp holds the reference callers' idioms verbatim (the saveGraph edge loop over
+    as_range (boost::edges (graph)), boost::tie, the 3- and 5-argument randomWalker with property maps, the three point
+    types of src/random_walker_segmentation.cpp:44): it must compile against include/tcs with plain g++."""
+    _build()
+    assert os.path.exists(REFCALL)
+
+
+@pytest.mark.gpu
+def test_reference_caller_code_runs():
+    _build()
+    r = subprocess.run([REFCALL], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "ref_caller_check ok" in r.stdout, r.stdout + r.stderr
+    # sparse colour ids, external maps, > 64 colours failing cleanly, the NaN seed, PointXYZ / PointXYZRGBA
+    assert "RandomWalkerSegmentation<PointXYZ>" in r.stdout and "NaN seed" in r.stdout
+    assert "distinct seed colours" in r.stderr

@@ -347,3 +347,23 @@ def test_one_ring_normals_bit_exact(ctx, scenes, name):
     o.normals(one_ring=True, mode=orc.MODE_FAST)
     assert np.count_nonzero(_bits(g.vertices()[2]) != _bits(o.vertices()[2])) <= 4 * 8
     g.close()
+
+
+@pytest.mark.parametrize("balancing", [capi.BALANCE_INVERSE, capi.BALANCE_GAUSSIAN_SQUARED, capi.BALANCE_LINEAR])
+@pytest.mark.parametrize("preset_cli", [False, True])
+def test_term_balancing_functions_bit_exact(ctx, scenes, balancing, preset_cli):
+    """EdgeWeightComputer::setTermBalancingFunction (graph/edge_weight_computer.h:325): the closed device set against
+    the oracle's restatement, all three normalisations (class preset: global; CLI preset: global + local + none)."""
+    g, o = _build_both(ctx, scenes["test13"], 0.006)
+    for h, mode in ((g, capi.MODE_PARITY), (o, orc.MODE_PARITY)):
+        h.normals(mode=mode)
+        h.signed_curvatures()
+    g.edge_weights(capi.TERMS_CLI if preset_cli else capi.TERMS_CLASS, mode=capi.MODE_PARITY, balancing=balancing)
+    o.edge_weights(orc.PRESET_CLI if preset_cli else orc.PRESET_CLASS, mode=orc.MODE_PARITY, balancing=balancing)
+    gw, ow = g.edges()[2], o.edges()[2]
+    # exp-based: CUDA's and glibc's float64 exp may differ in the last float64 bit (survives rounding with p ~ 2^-29)
+    assert np.count_nonzero(_bits(gw) != _bits(ow)) <= (2 if balancing == capi.BALANCE_GAUSSIAN_SQUARED else 0)
+    # and it is a different weighting from the default Gaussian
+    g.edge_weights(capi.TERMS_CLI if preset_cli else capi.TERMS_CLASS, mode=capi.MODE_PARITY)
+    assert np.count_nonzero(_bits(g.edges()[2]) != _bits(gw)) > len(gw) // 2
+    g.close()
