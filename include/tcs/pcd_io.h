@@ -146,9 +146,20 @@ inline Table read(const std::string& path) {
     f.type = types[i][0];
     f.count = i < counts.size() ? std::atoi(counts[i].c_str()) : 1;
     if (f.size != 1 && f.size != 2 && f.size != 4 && f.size != 8) throw std::runtime_error(path + ": bad field size");
-    rec += (size_t)f.size * f.count;
+    if (f.count <= 0 || f.count > (1 << 20)) throw std::runtime_error(path + ": bad field count");
+    if (f.type != 'F' && f.type != 'U' && f.type != 'I') throw std::runtime_error(path + ": bad field type");
+    rec += (size_t)f.size * (size_t)f.count;
     t.fields.push_back(f);
   }
+  // The header is untrusted: POINTS / WIDTH x HEIGHT decide how much is allocated and copied, so they are bounded by
+  // what the file can hold before anything is sized from them (every point takes at least one byte of data in ascii
+  // and binary; an LZF stream expands by at most ~255x, checked again against the stream's own size field below).
+  const size_t data_bytes = blob.size() >= pos ? blob.size() - pos : 0;
+  if (rec == 0 || t.n > std::numeric_limits<size_t>::max() / rec) throw std::runtime_error(path + ": POINTS x record size overflows");
+  if (mode == "binary" && rec * t.n > data_bytes) throw std::runtime_error(path + ": binary data ends early");
+  if (mode == "ascii" && t.n > data_bytes) throw std::runtime_error(path + ": ascii data ends early");
+  if (mode == "binary_compressed" && (data_bytes < 8 || rec * t.n / 256 > data_bytes)) throw std::runtime_error(path + ": compressed data ends early");
+  if (mode != "ascii" && mode != "binary" && mode != "binary_compressed") throw std::runtime_error(path + ": unknown DATA mode '" + mode + "'");
   t.data.resize(t.fields.size());
   for (size_t i = 0; i < t.fields.size(); ++i) t.data[i].assign(t.n * t.fields[i].size * t.fields[i].count, 0);
   const unsigned char* p = (const unsigned char*)blob.data() + pos;

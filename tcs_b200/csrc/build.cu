@@ -282,6 +282,9 @@ __global__ void k_probe(const uint32_t* __restrict__ keys, size_t V, const unsig
     const int dx = d / 9 - 1, dy = (d / 3) % 3 - 1, dz = d % 3 - 1;
     uint32_t u = TCS_NIL;
     bool skip = (d == 13) || (dx < 0 && kx == 0) || (dy < 0 && ky == 0) || (dz < 0 && kz == 0);
+    // depth 21: a component at 2^21 - 1 has no +1 neighbour inside the tree, and its 21-bit field would carry into the
+    // next axis of the packed key (aliasing (kx, 2^21, kz) with (kx + 1, 0, kz))
+    skip = skip || (dx > 0 && kx == 0x1FFFFFu) || (dy > 0 && ky == 0x1FFFFFu) || (dz > 0 && kz == 0x1FFFFFu);
     if (!skip) {
       uint64_t k = (uint64_t)(kx + dx) << 42 | (uint64_t)(ky + dy) << 21 | (uint64_t)(kz + dz);
       u = hash_find(tkey, tval, mask, k);

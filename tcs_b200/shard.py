@@ -57,11 +57,13 @@ def merge_best(best_val, best_col):
     val = np.asarray(best_val, np.float32)
     col = np.asarray(best_col, np.uint32)
     # largest potential wins; among equal potentials the lowest non-zero colour (colour 0 = unlabelled in that shard)
+    # A vertex is labelled iff SOME shard labelled it (colour > 0: one of its potentials is non-zero - the rule of the
+    # single-GPU k_argmax, which does not look at the sign); shards that left it unlabelled do not compete.
     key = np.where(col > 0, col, np.uint32(0xFFFFFFFF))
+    val = np.where(col > 0, val, -np.inf)
     order = np.lexsort((key, -val), axis=0)[0]          # per vertex: shard with max val, then min colour
-    v = np.take_along_axis(val, order[None, :], axis=0)[0]
     c = np.take_along_axis(col, order[None, :], axis=0)[0]
-    return np.where(v > 0, c, 0).astype(np.uint32)
+    return c.astype(np.uint32)
 
 
 def all_gather_best(val, col, world: int):
@@ -124,9 +126,10 @@ def _merge_best_nccl(val, col, world: int):
     gc = torch.empty((world,) + tc.shape, dtype=tc.dtype, device="cuda")
     dist.all_gather_into_tensor(gv, tv)
     dist.all_gather_into_tensor(gc, tc)
+    gv = torch.where(gc > 0, gv, torch.full_like(gv, float("-inf")))   # unlabelled in a shard: does not compete
     best = gv.max(dim=0).values
     big = torch.iinfo(torch.int32).max
     cand = torch.where((gv == best[None, :]) & (gc > 0), gc, torch.full_like(gc, big))
     c = cand.min(dim=0).values
-    c = torch.where((best > 0) & (c != big), c, torch.zeros_like(c))
+    c = torch.where(c != big, c, torch.zeros_like(c))
     return c.cpu().numpy().view(np.uint32)

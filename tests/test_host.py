@@ -151,6 +151,11 @@ def test_column_shard_blocks_and_merge():
     col = np.array([[1, 2, 0, 2], [3, 4, 0, 3]], np.uint32)
     assert list(shard.merge_best(val, col)) == [1, 2, 0, 3]
     assert list(shard.merge_best(val[::-1], col[::-1])) == [1, 2, 0, 3]
+    # a vertex whose best potential is <= 0 (tiny negative PCG values) is still labelled when a shard labelled it, like on
+    # one GPU (k_argmax labels every row with a non-zero potential); a shard that left it unlabelled does not compete
+    val = np.array([[-1e-9, 0.0, -2e-9], [0.0, 0.0, -1e-9]], np.float32)
+    col = np.array([[2, 0, 1], [0, 0, 3]], np.uint32)
+    assert list(shard.merge_best(val, col)) == [2, 0, 3]
 
 
 def test_all_gather_best_world_size_2_gloo(tmp_path):

@@ -186,3 +186,24 @@ def test_app_nearest_neighbour_builders(scenes, tmp_path, builder):
     want = np.where(p2v == 0xFFFFFFFF, 0, cg[np.minimum(p2v, g.V - 1)])
     assert np.count_nonzero(got["label"] != want) <= 3
     ctx.close()
+
+
+@pytest.mark.parametrize("header", [
+    "POINTS 4611686018427387905\nDATA binary\n",            # 2^62 + 1: points x record size wraps around size_t
+    "POINTS 1000000\nDATA binary\n",                         # more points than the file holds
+    "POINTS 1000000\nDATA ascii\n",
+    "POINTS 4000000000\nDATA binary_compressed\n",
+    "POINTS 2\nDATA binary\n",                               # valid sizes but COUNT 0 / -1 below
+])
+def test_pcd_reader_rejects_crafted_headers(tmp_path, header):
+    """include/tcs/pcd_io.h trusts nothing in the header: oversized POINTS, wrapped products and non-positive COUNT end in
+    an error message and exit code, not in an out-of-bounds write (run through the evaluation tool, which reads PCDs)."""
+    _build()
+    count = "0 -1" if header.startswith("POINTS 2\n") else "1 1"
+    path = str(tmp_path / "bad.pcd")
+    with open(path, "wb") as f:
+        f.write(("# .PCD v0.7\nVERSION 0.7\nFIELDS x label\nSIZE 4 4\nTYPE F U\nCOUNT %s\nWIDTH 2\nHEIGHT 1\n%s" % (count, header)).encode())
+        f.write(b"\0" * 16)
+    r = subprocess.run([EVAL, path, path], capture_output=True, text=True, timeout=60)
+    assert r.returncode not in (0, -11, -6) and r.returncode > 0, (r.returncode, r.stderr)
+    assert "bad.pcd" in r.stderr
