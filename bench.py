@@ -323,8 +323,8 @@ def run_c4(args, rank, local_rank, world):
     def merge(graph):
         """The column shard's one exchange: all-gather of (best potential, colour) per vertex over NCCL."""
         if columns:
-            val, col = graph.best()
-            shard._merge_best_nccl(val, col, world)
+            tv, tc = graph.best_device()          # device-resident: no host staging before the all-gather
+            shard._merge_best_nccl(tv, tc, world)
 
     def scene_of(step):
         return 0 if columns else (rank + step) % S

@@ -225,6 +225,10 @@ int tcs_graph_download_best(tcs_graph* g, float* best_potential, uint32_t* best_
 /* device-resident results (valid until the graph is destroyed) */
 const uint32_t* tcs_graph_d_colours(const tcs_graph* g);
 const int32_t* tcs_graph_d_point_cluster(const tcs_graph* g);
+/* V floats: the device copy of tcs_graph_download_best's best_potential (its colours are tcs_graph_d_colours) - what a
+ * label-column shard hands to the all-gather without staging through the host.  Written on the context stream:
+ * tcs_ctx_synchronize before another stream or library reads it. */
+const float* tcs_graph_d_best_potential(const tcs_graph* g);
 
 /* ---- measurement hooks (bench.py): the CG SpMM kernel alone on the assembled system of the last solve ----- */
 /* launches the SpMM `reps` times on the context stream between two CUDA events; returns average ms per launch */

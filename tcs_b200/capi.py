@@ -40,7 +40,7 @@ EXPORTS = [
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
     "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm", "tcs_graph_download_best",
-    "tcs_build_nn_graph", "tcs_segment_batch", "tcs_nearest_vertices_noalloc", "tcs_edge_weights_ex",
+    "tcs_graph_d_best_potential", "tcs_build_nn_graph", "tcs_segment_batch", "tcs_nearest_vertices_noalloc", "tcs_edge_weights_ex",
 ]
 
 
@@ -143,12 +143,24 @@ def lib():
     L.tcs_graph_d_colours.restype = vp
     L.tcs_graph_d_point_cluster.argtypes = [vp]
     L.tcs_graph_d_point_cluster.restype = vp
+    L.tcs_graph_d_best_potential.argtypes = [vp]
+    L.tcs_graph_d_best_potential.restype = vp
     L.tcs_bench_spmm.argtypes = [vp, ci, C.POINTER(cf), C.POINTER(C.c_longlong)]
     L.tcs_graph_download_best.argtypes = [vp, vp, vp]
     L.tcs_check_spmm.argtypes = [vp, C.c_uint, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                  C.POINTER(ci)]
     _lib = L
     return L
+
+
+class _DeviceSpan:
+    """a borrowed device buffer for torch.as_tensor (CUDA array interface v2)"""
+
+    def __init__(self, ptr, count, typestr):
+        if not ptr:
+            raise TcsError(ERR_STATE, "no device buffer (no solve on this graph yet)")
+        self.__cuda_array_interface__ = dict(shape=(int(count),), typestr=typestr, data=(int(ptr), False), version=2,
+                                             strides=None)
 
 
 def _p(a):
@@ -179,7 +191,7 @@ class Context:
         st = lib().tcs_ctx_create_on_stream(device, C.c_void_p(stream) if stream else None, C.byref(h))
         if st != OK:
             raise TcsError(st, (lib().tcs_last_error(None) or b"").decode())
-        self.h = h
+        self.h, self.device = h, int(device)
 
     def close(self):
         if getattr(self, "h", None):
@@ -410,6 +422,16 @@ class Graph:
         """(best potential, its colour) per vertex among the columns this solve covered."""
         val, col = np.zeros(self.V, np.float32), np.zeros(self.V, np.uint32)
         self.ctx.check(lib().tcs_graph_download_best(self.h, _p(val), _p(col)))
+        return val, col
+
+    def best_device(self):
+        """(best potential f32, its colour as int32) as torch CUDA tensors aliasing the graph's device buffers - no copy,
+        no host staging; valid while the graph lives.  Synchronizes the context stream first (torch reads on its own)."""
+        import torch
+        self.ctx.synchronize()
+        V, dev = self.V, self.ctx.device
+        val = torch.as_tensor(_DeviceSpan(lib().tcs_graph_d_best_potential(self.h), V, "<f4"), device="cuda:%d" % dev)
+        col = torch.as_tensor(_DeviceSpan(lib().tcs_graph_d_colours(self.h), V, "<i4"), device="cuda:%d" % dev)
         return val, col
 
     def check_spmm(self, seed=1):

@@ -285,3 +285,4 @@ extern "C" int tcs_graph_download_potentials(tcs_graph* g, float* potentials) {
 
 extern "C" const uint32_t* tcs_graph_d_colours(const tcs_graph* g) { return g ? g->colours.p : nullptr; }
 extern "C" const int32_t* tcs_graph_d_point_cluster(const tcs_graph* g) { return g ? g->point_cluster.p : nullptr; }
+extern "C" const float* tcs_graph_d_best_potential(const tcs_graph* g) { return g ? g->best_val.p : nullptr; }

@@ -97,8 +97,7 @@ def segment_cloud_column_sharded(ctx, resolution, seed_xyz, seed_label, rank: in
         r = None
     else:
         r = ctx.segment_cloud(resolution, seed_xyz, seed_label, preset=preset, mode=mode, opts=opts)
-        val, col = r["graph"].best()
-        V = len(val)
+        V = r["graph"].V
     if world > 1:
         import torch
         import torch.distributed as dist
@@ -106,22 +105,28 @@ def segment_cloud_column_sharded(ctx, resolution, seed_xyz, seed_label, rank: in
         t = torch.tensor([V or 0], dtype=torch.int64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         V = int(t.item())
-    if r is None:
-        val, col = np.zeros(V, np.float32), np.zeros(V, np.uint32)
     if world > 1:
         import torch.distributed as dist
-        if dist.get_backend() == "nccl":      # merge on the device: 8 bytes x V x world, one pass
-            return _merge_best_nccl(val, col, world), r
+        if dist.get_backend() == "nccl":
+            # device-resident exchange: the all-gather reads the graph's own (best potential, colour) buffers - no
+            # host staging; 8 bytes x V per rank over NVLink, then one merge pass on the device
+            import torch
+            if r is None:
+                dev = torch.device("cuda", ctx.device)
+                tv, tc = torch.zeros(V, dtype=torch.float32, device=dev), torch.zeros(V, dtype=torch.int32, device=dev)
+            else:
+                tv, tc = r["graph"].best_device()
+            return _merge_best_nccl(tv, tc, world), r
+    val, col = (np.zeros(V, np.float32), np.zeros(V, np.uint32)) if r is None else r["graph"].best()
     gv, gc = all_gather_best(val, col, world)
     return merge_best(gv, gc), r
 
 
-def _merge_best_nccl(val, col, world: int):
+def _merge_best_nccl(tv, tc, world: int):
+    """tv (V,) f32 / tc (V,) i32 CUDA tensors of this rank -> merged (V,) uint32 colours on the host"""
     import numpy as np
     import torch
     import torch.distributed as dist
-    tv = torch.from_numpy(np.ascontiguousarray(val, np.float32)).cuda()
-    tc = torch.from_numpy(np.ascontiguousarray(col, np.uint32).view(np.int32)).cuda()
     gv = torch.empty((world,) + tv.shape, dtype=tv.dtype, device="cuda")
     gc = torch.empty((world,) + tc.shape, dtype=tc.dtype, device="cuda")
     dist.all_gather_into_tensor(gv, tv)

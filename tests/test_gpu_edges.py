@@ -309,6 +309,56 @@ dist.destroy_process_group()
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
 
 
+def test_label_column_shard_device_resident_merge_over_nccl(tmp_path):
+    """The NCCL leg of the column shard reads the graph's own device buffers (tcs_graph_d_best_potential /
+    tcs_graph_d_colours, no host staging): one rank per visible GPU (up to 2; a world of 1 on a one-GPU box still
+    goes through ncclAllGather and the device merge)."""
+    import os, subprocess, sys
+    import torch
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    nproc = min(2, torch.cuda.device_count())
+    script = tmp_path / "w.py"
+    script.write_text('''
+import os, sys
+sys.path.insert(0, %r)
+import numpy as np, torch, torch.distributed as dist
+from tcs_b200 import capi, shard
+from tcs_b200.seeds import seeds_from_labels
+local = int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+rank, world = dist.get_rank(), dist.get_world_size()
+d = np.load(os.path.join(%r, "tests", "golden", "scene_test56.npz"))     # 18 labels
+sx, sl, _ = seeds_from_labels(d["xyz"], d["label"], 3, 5)
+ctx = capi.Context(local)
+ctx.upload_cloud(d["xyz"], d["rgba"])
+opts = capi.default_opts()
+opts.column_begin, opts.column_count = shard.columns_for_rank(len(np.unique(sl)), rank, world)
+r = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY, opts=opts)
+tv, tc = r["graph"].best_device()
+val, col = r["graph"].best()
+assert tv.is_cuda and tv.device.index == local and np.array_equal(tv.cpu().numpy(), val)
+assert np.array_equal(tc.cpu().numpy().view(np.uint32), col)
+merged = shard._merge_best_nccl(tv, tc, world)
+gv, gc = shard.all_gather_best(val, col, world)
+assert np.array_equal(merged, shard.merge_best(gv, gc))
+if world > 1:
+    again, _ = shard.segment_cloud_column_sharded(ctx, 0.006, sx, sl, rank, world, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
+    assert np.array_equal(again, merged)
+if rank == 0:
+    full = ctx.segment_cloud(0.006, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_PARITY)
+    bad = int(np.count_nonzero(merged != full["vertex_colour"]))
+    assert bad <= max(3, len(merged) // 2000), bad
+    print("world", world, "merged labels differ on", bad, "of", len(merged))
+dist.barrier()
+dist.destroy_process_group()
+''' % (root, root))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
+                        "--master-addr", "127.0.0.1", "--master-port", "29547", str(script)],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+
+
 @pytest.fixture
 def coarse_env():
     """Switches of the multilevel preconditioner (csrc/amg.cuh), restored after the test."""
