@@ -55,12 +55,16 @@ def parse():
     ap.add_argument("--scenes", type=int, default=1024, help="c5: scenes of the whole job")
     ap.add_argument("--distinct", type=int, default=128, help="c5: distinct generated scenes (cycled to fill the job)")
     ap.add_argument("--batch", type=int, default=32, help="c5: scenes per tcs_segment_batch call")
+    ap.add_argument("--contexts", type=int, default=3, help="c5: worker contexts (streams) per GPU, batches round-robin over them")
     ap.add_argument("--cpu-procs", type=int, default=0, help="reference arm: worker processes (0 = all host cores, at most 32)")
     ap.add_argument("--shard", default="scenes", choices=["scenes", "columns"],
                     help="c4, N > 1: 'scenes' = one scene per GPU (weak scaling, no collective, the default); 'columns' = ONE "
                          "scene, its label columns split over the GPUs, one NCCL all-gather of (best potential, colour) "
                          "per vertex (strong scaling)")
     return ap.parse_args()
+
+
+C4_ROTATION = 2
 
 
 def c4_scene(args, index):
@@ -93,27 +97,70 @@ def c5_scene(index):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and throttle reasons of this rank's GPU, sampled DURING the timed region (B200_PROFILING.md's clocks
+    line).  Reads NVML in-process (nvidia_ml_py): a spawned `nvidia-smi` takes a driver lock long enough to stall the
+    host-synchronised CG loop for ~100 ms per query.  Falls back to nvidia-smi (sparse) only if NVML cannot be loaded.
+    The thread idles until arm() and records nothing after disarm()."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self._halt = index, [], threading.Event()
+        self.index, self.rows, self._halt, self._armed = index, [], threading.Event(), threading.Event()
+        self.nv, self.h, self.source = None, None, "nvidia-smi"
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            try:
+                uuid = "GPU-" + str(torch.cuda.get_device_properties(index).uuid)
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode())
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+                ids = [v for v in vis.split(",") if v.strip()]
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(int(ids[index]) if ids and ids[index].strip().isdigit() else index)
+            self.nv, self.source = pynvml, "nvml"
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nv = None
+
+    def arm(self):
+        self._armed.set()
+
+    def disarm(self):
+        self._armed.clear()
+
+    def _sample_nvml(self):
+        nv = self.nv
+        mhz = float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+        try:
+            mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+        except Exception:
+            mask = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+        flags = [(nv.nvmlClocksThrottleReasonHwSlowdown, "hw_slowdown"), (nv.nvmlClocksThrottleReasonHwThermalSlowdown, "hw_thermal_slowdown"),
+                 (nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_thermal_slowdown"), (nv.nvmlClocksThrottleReasonSwPowerCap, "sw_power_cap")]
+        return [str(mhz), str(self.max_mhz)] + ["Active" if mask & bit else "Not Active" for bit, _ in flags]
 
     def run(self):
         while not self._halt.is_set():
+            if not self._armed.is_set():
+                self._halt.wait(0.005)
+                continue
             try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in out.strip().split(",")])
+                if self.nv is not None:
+                    self.rows.append(self._sample_nvml())
+                else:
+                    out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                    self.rows.append([c.strip() for c in out.strip().split(",")])
             except Exception:
                 pass
-            self._halt.wait(1.0)   # nvidia-smi queries perturb the GPU: sample sparsely
+            self._halt.wait(0.05 if self.nv is not None else 1.0)
 
     def stop(self):
         self._halt.set()
-        self.join(timeout=6)
+        if self.is_alive():
+            self.join(timeout=6)
         sm, mx, reasons = [], 0.0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in self.rows:
@@ -125,8 +172,8 @@ class ClockSampler(threading.Thread):
                         reasons.add(n)
             except Exception:
                 continue
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_min_mhz": min(sm) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm), "source": self.source + ", sampled inside the timed region only"}
 
 
 def peaks():
@@ -301,7 +348,9 @@ def run_c4(args, rank, local_rank, world):
     torch, dist, barrier = _dist_setup(local_rank, world)
     from tcs_b200 import capi
     columns = args.shard == "columns" and world > 1
-    S = 1 if columns else min(world, 4)            # distinct scenes of the rotation
+    # distinct scenes of the rotation: the same set at every N (N = 1 included), so that every rank of every N does the
+    # same mix of work per pair of steps and the per-N values are comparable (scene 0: 136 CG iterations, scene 1: 200)
+    S = 1 if columns else C4_ROTATION
     mine = sorted({(rank + s) % S for s in range(S)}) if not columns else [0]
     scenes = {k: c4_scene(args, k) for k in mine}
     stream = torch.cuda.Stream()
@@ -355,7 +404,7 @@ def run_c4(args, rank, local_rank, world):
         merge(g)
         return dict(graph=g, info=info)
 
-    def timed(step_fn):
+    def timed(step_fn, sampler=None):
         """W warm-up steps (every scene of the rotation at least once), then K steps between two events."""
         for s in range(max(args.warmup, S)):
             step_fn(s)["graph"].close()
@@ -363,21 +412,31 @@ def run_c4(args, rank, local_rank, world):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         infos, V, E = [], 0, 0
         launches0 = ctx.launches
+        if sampler:
+            sampler.arm()
         with torch.cuda.stream(stream):
             ev0.record(stream)
             for s in range(args.steps):
+                t_host = time.perf_counter()
                 r = step_fn(s)
                 infos.append(r["info"].as_dict())
+                if os.environ.get("TCS_BENCH_DEBUG"):
+                    print("[rank %d] step %d: host %.1f ms, iterations %d, stage_ms %s" % (
+                        rank, s, 1e3 * (time.perf_counter() - t_host), infos[-1]["iterations"],
+                        [round(x, 1) for x in infos[-1]["stage_ms"][:12]]), file=sys.stderr, flush=True)
                 V += r["graph"].V
                 E = r["graph"].E
                 r["graph"].close()
             ev1.record(stream)
         barrier()
+        if sampler:
+            sampler.disarm()
         return ev0.elapsed_time(ev1), infos, V, E, ctx.launches - launches0
 
     sampler = ClockSampler(local_rank)
-    sampler.start()
-    ms, infos, V, E, launches = timed(step_resident)
+    if not os.environ.get("TCS_BENCH_NO_CLOCKS"):
+        sampler.start()
+    ms, infos, V, E, launches = timed(step_resident, sampler)
     clocks = sampler.stop()
     ms_e2e, infos_e, Ve, _, launches_e = timed(step_e2e)
     its = [i["iterations"] for i in infos]
@@ -480,19 +539,26 @@ def run_c5(args, rank, local_rank, world):
     distinct = sorted({j % D for j in mine})
     data = {k: c5_scene(k) for k in distinct}
     n = 640 * 480
-    stream = torch.cuda.Stream()
-    ctx = capi.Context(local_rank, stream=stream.cuda_stream)
+    # W worker contexts (one stream each) share the GPU: while one batch is in its bandwidth-bound solve, another
+    # worker's batch runs its launch-bound graph / hierarchy stages and its copies - the same scheme as the C++ driver
+    # (include/tcs/batch_segmenter.h).  Batch i belongs to worker i mod W.
+    W = max(1, args.contexts)
+    streams = [torch.cuda.Stream() for _ in range(W)]
+    fence = torch.cuda.Stream()
+    ctxs = [capi.Context(local_rank, stream=st.cuda_stream) for st in streams]
+    ctx = ctxs[0]
     host = {k: _pinned_records(torch, data[k][0], data[k][1]) for k in distinct}
     dev = {k: host[k].to("cuda", non_blocking=False) for k in distinct}
     seeds = {k: (np.ascontiguousarray(data[k][2], np.float32), np.ascontiguousarray(data[k][3], np.uint32)) for k in distinct}
     B = max(1, args.batch)
-    pc_host = torch.empty((B, n), dtype=torch.int32).pin_memory()
-    vc_host = torch.empty((B, n), dtype=torch.int32).pin_memory()
-    opts = capi.default_opts(time_spmm=1)
+    pc_host = [torch.empty((B, n), dtype=torch.int32).pin_memory() for _ in range(W)]
+    vc_host = [torch.empty((B, n), dtype=torch.int32).pin_memory() for _ in range(W)]
+    opts = capi.default_opts(time_spmm=0)
+    opts_timed = capi.default_opts(time_spmm=1)
 
     def make_batches(resident):
         out = []
-        for b0 in range(0, len(mine), B):
+        for i, b0 in enumerate(range(0, len(mine), B)):
             ids = mine[b0:b0 + B]
             arr = (capi.Scene * len(ids))()
             for slot, j in enumerate(ids):
@@ -505,48 +571,75 @@ def run_c5(args, rank, local_rank, world):
                 else:
                     base = host[k].data_ptr()
                     a.xyz, a.xyz_stride, a.rgba, a.rgba_stride = base, 16, base + 12, 16
-                    a.point_cluster = pc_host.data_ptr() + slot * n * 4
-                    a.vertex_colour = vc_host.data_ptr() + slot * n * 4
+                    a.point_cluster = pc_host[i % W].data_ptr() + slot * n * 4
+                    a.vertex_colour = vc_host[i % W].data_ptr() + slot * n * 4
             out.append(arr)
         return out
 
-    def job(batches):
-        """One step = this rank's share of the job.  Returns (vertices, scenes, per-batch infos)."""
-        V, infos = 0, []
-        for arr in batches:
-            info = capi.SolveInfo()
-            ctx.check(L.tcs_segment_batch(ctx.h, arr, len(arr), C5_RES, capi.PRESET_CLASS, capi.MODE_FAST, C.byref(opts),
-                                          C.byref(info)))
-            V += sum(a.V for a in arr)
-            infos.append(info.as_dict())
-        return V, infos
+    def run_batch(c, arr, o):
+        info = capi.SolveInfo()
+        c.check(L.tcs_segment_batch(c.h, arr, len(arr), C5_RES, capi.PRESET_CLASS, capi.MODE_FAST, C.byref(o), C.byref(info)))
+        return sum(a.V for a in arr), info.as_dict()
 
-    def timed(batches):
+    def job(batches):
+        """One step = this rank's share of the job.  Returns (vertices, per-batch infos)."""
+        res, errs = [[] for _ in range(W)], []
+
+        def worker(w):
+            try:
+                torch.cuda.set_device(local_rank)
+                for arr in batches[w::W]:
+                    res[w].append(run_batch(ctxs[w], arr, opts))
+            except Exception as e:       # surfaced below: a failing batch must fail the bench
+                errs.append(e)
+
+        th = [threading.Thread(target=worker, args=(w,)) for w in range(W)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        if errs:
+            raise errs[0]
+        flat = [r for w in range(W) for r in res[w]]
+        return sum(r[0] for r in flat), [r[1] for r in flat]
+
+    def timed(batches, sampler=None):
         for _ in range(args.warmup):
             job(batches)
         barrier()
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         V, infos = 0, []
-        launches0 = ctx.launches
-        with torch.cuda.stream(stream):
-            ev0.record(stream)
-            for _ in range(args.steps):
-                v, inf = job(batches)
-                V += v
-                infos += inf
-            ev1.record(stream)
+        launches0 = sum(c.launches for c in ctxs)
+        if sampler:
+            sampler.arm()
+        ev0.record(fence)
+        for st in streams:
+            st.wait_event(ev0)
+        for _ in range(args.steps):
+            v, inf = job(batches)
+            V += v
+            infos += inf
+        for st in streams:                 # the step ends when the slowest worker stream has drained
+            e = torch.cuda.Event()
+            e.record(st)
+            fence.wait_event(e)
+        ev1.record(fence)
         barrier()
-        return ev0.elapsed_time(ev1), V, infos, ctx.launches - launches0
+        if sampler:
+            sampler.disarm()
+        return ev0.elapsed_time(ev1), V, infos, sum(c.launches for c in ctxs) - launches0
 
     sampler = ClockSampler(local_rank)
     sampler.start()
-    ms, V, infos, launches = timed(make_batches(True))
+    ms, V, infos, launches = timed(make_batches(True), sampler)
     clocks = sampler.stop()
     ms_e2e, Ve, infos_e, launches_e = timed(make_batches(False))
+    # the SpMM of one batch timed ALONE (one context, nothing else on the GPU): the roofline's kernel time
+    alone = [run_batch(ctx, arr, opts_timed)[1] for arr in make_batches(True)[:4]]
     (ms_max, ms_e2e_max), (V_all, Ve_all, launches_all, scenes_all) = _reduce(
         torch, dist, world, [ms, ms_e2e], [float(V), float(Ve), float(launches + launches_e), float(len(mine))])
     if rank == 0:
-        full = [i for i in infos if i["rows"] == max(j["rows"] for j in infos)] or infos
+        full = [i for i in alone if i["rows"] == max(j["rows"] for j in alone)] or alone
         info = full[0]
         nrows, nnz, K = info["rows"], info["nnz"], info["ncolours"]
         b_spmm = 8 * nnz + 4 * (nrows + 1) + 8 * nrows * K
@@ -565,7 +658,7 @@ def run_c5(args, rank, local_rank, world):
                            scenes_per_s=scenes_all * args.steps / (ms_max * 1e-3),
                            scenes_per_s_e2e=scenes_all * args.steps / (ms_e2e_max * 1e-3),
                            vertices_per_scene=int(V // args.steps // max(1, len(mine))), batch_rows=nrows, batch_nnz=nnz, labels=K,
-                           pcg_iterations_per_batch_rank0=its, converged=all(i["converged"] for i in infos),
+                           contexts_per_gpu=W, pcg_iterations_per_batch_rank0=its, converged=all(i["converged"] for i in infos),
                            max_rel_residual=max(max(i["rel_residual"]) for i in infos),
                            preconditioner="Jacobi + V(1,1) cycle on a device-built aggregation hierarchy of the merged "
                                           "block-diagonal system; one CG recurrence per (scene, column)"),
@@ -578,7 +671,9 @@ def run_c5(args, rank, local_rank, world):
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak if peak else None,
                          "traffic": None, "frac_nominal": achieved / NOMINAL_HBM_GBS, "algorithmic_bytes_per_launch": b_spmm,
                          "avg_launch_ms": avg_ms, "launches_per_step": sum(i["spmm_launches"] for i in infos) // args.steps,
-                         "spmm_share_of_step": sum(i["spmm_ms"] for i in infos) / ms if ms else None, "peak_source": peak_src},
+                         "spmm_share_of_solve": (avg_ms * full[0]["iterations"] / full[0]["stage_ms"][9]) if full[0]["stage_ms"][9] else None,
+                         "timed": "one batch alone on the GPU, outside the timed region (the step overlaps %d contexts)" % W,
+                         "peak_source": peak_src},
             "stage_ms_first_batch": {"graphs_features_systems": round(infos[0]["stage_ms"][0], 3), "merge": round(infos[0]["stage_ms"][8], 3),
                                      "solve": round(infos[0]["stage_ms"][9], 3), "labels_and_copies": round(infos[0]["stage_ms"][10], 3)},
         }
@@ -612,7 +707,8 @@ def run_c5(args, rank, local_rank, world):
                              "vertices": int(vs), "mismatches": mism, "near_ties": near, "max_oracle_top2_gap": worst,
                              "bound": label_gate.NEAR_TIE_GAP}
         print(json.dumps(out), flush=True)
-    ctx.close()
+    for c in ctxs:
+        c.close()
     if world > 1:
         dist.destroy_process_group()
 

@@ -578,12 +578,8 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Hierarchy& H) {
     TRY(E.alloc(ctx, (size_t)H.m * H.m)); TRY(H.Einv.alloc(ctx, (size_t)H.m * H.m));
     LAUNCH(ctx, k_dense_build, div_up(H.m, 128), 128, 0, H.m, B.A.rowptr, B.A.col, B.A.val, B.g.p, E.p);
     const size_t smem = ((size_t)H.m * H.m + H.m) * sizeof(double);
-    static bool attr_set = false;
-    if (!attr_set) {
-      CK(cudaFuncSetAttribute(k_dense_invert, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)(((size_t)kBottomMax * kBottomMax + kBottomMax) * sizeof(double))));
-      attr_set = true;
-    }
+    // function attributes are per device: set on every plan (cheap), not once per process
+    CK(cudaFuncSetAttribute(k_dense_invert, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(((size_t)kBottomMax * kBottomMax + kBottomMax) * sizeof(double))));
     LAUNCH(ctx, k_dense_invert, 1, 1024, smem, H.m, E.p, H.Einv.p);
     CK(cudaStreamSynchronize(ctx->stream));  // E is a local buffer
   }

@@ -798,11 +798,8 @@ int spmm_plan(tcs_ctx* ctx, tcs_system& S) {
     if (getenv("TCS_DEBUG")) fprintf(stderr, "[tcs] spmm tiled: far buffer of %u rows does not fit, using v1\n", max_far);
     return TCS_OK;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    CK(cudaFuncSetAttribute(k_spmm_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
-    attr_set = true;
-  }
+  // function attributes are per device: set on every plan (cheap), not once per process
+  CK(cudaFuncSetAttribute(k_spmm_tiled, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
   S.tile = T;
   S.tiled = true;
   if (getenv("TCS_DEBUG"))
@@ -944,11 +941,8 @@ int spmm_plan_ring(tcs_ctx* ctx, tcs_system& S) {
          tile_start.p, S.cv.p, S.ring_blob.p);
   S.cv.release();  // plan-time scratch only: the ring kernel reads ring_meta + ring_blob
   S.ring_entries = total_entries;
-  static bool attr_set = false;
-  if (!attr_set) {
-    CK(cudaFuncSetAttribute(k_spmm_ring, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
-    attr_set = true;
-  }
+  // function attributes are per device: set on every plan (cheap), not once per process
+  CK(cudaFuncSetAttribute(k_spmm_ring, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
   S.rg = T;
   // Contiguous tile ranges of equal work.  First guess: a tile costs its entries + far rows + a per-row prologue.
   // Then the kernel itself is the cost model: it reports every CTA's cycles, the tiles of a CTA are re-weighted by
