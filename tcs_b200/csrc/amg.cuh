@@ -364,23 +364,25 @@ __global__ void __launch_bounds__(256) k_level_spmm(int n, int Q, const uint32_t
       const float4 x = X[i];
       const float4 b = RHS[i];
       const float d = gdiag[row];
-      float4 y = make_float4(d * x.x, d * x.y, d * x.z, d * x.w);
+      const F4p xp = f4_pack(x);
+      F4p yy = f4_pack(make_float4(d * x.x, d * x.y, d * x.z, d * x.w));
       for (; a + 4 <= a1; a += 4) {
         const int c0 = col[a], c1 = col[a + 1], c2 = col[a + 2], c3 = col[a + 3];
         const float w0 = val[a], w1 = val[a + 1], w2 = val[a + 2], w3 = val[a + 3];
         const float4 t0 = X[(size_t)c0 * Q + q], t1 = X[(size_t)c1 * Q + q];
         const float4 t2 = X[(size_t)c2 * Q + q], t3 = X[(size_t)c3 * Q + q];
-        y.x += w0 * (t0.x - x.x); y.y += w0 * (t0.y - x.y); y.z += w0 * (t0.z - x.z); y.w += w0 * (t0.w - x.w);
-        y.x += w1 * (t1.x - x.x); y.y += w1 * (t1.y - x.y); y.z += w1 * (t1.z - x.z); y.w += w1 * (t1.w - x.w);
-        y.x += w2 * (t2.x - x.x); y.y += w2 * (t2.y - x.y); y.z += w2 * (t2.z - x.z); y.w += w2 * (t2.w - x.w);
-        y.x += w3 * (t3.x - x.x); y.y += w3 * (t3.y - x.y); y.z += w3 * (t3.z - x.z); y.w += w3 * (t3.w - x.w);
+        f4_diff_fma(yy, w0, t0, xp);
+        f4_diff_fma(yy, w1, t1, xp);
+        f4_diff_fma(yy, w2, t2, xp);
+        f4_diff_fma(yy, w3, t3, xp);
       }
       for (; a < a1; ++a) {
         const int c = col[a];
         const float w = val[a];
         const float4 t = X[(size_t)c * Q + q];
-        y.x += w * (t.x - x.x); y.y += w * (t.y - x.y); y.z += w * (t.z - x.z); y.w += w * (t.w - x.w);
+        f4_diff_fma(yy, w, t, xp);
       }
+      const float4 y = f4_unpack(yy);
       float4 o = make_float4(b.x - y.x, b.y - y.y, b.z - y.z, b.w - y.w);
       if (SMOOTH) {
         const float wd = winvd[row];

@@ -184,6 +184,32 @@ static inline unsigned div_up(size_t a, unsigned b) { return (unsigned)((a + b -
     (ctx)->launches++;                                                     \
   } while (0)
 
+// ---- packed float pairs: sm_100 executes two IEEE float operations per issue slot (FADD2 / FFMA2, PTX add/sub/fma
+// .f32x2) - the same roundings as the scalar instructions, half the issue slots.  The SpMM kernels are issue-bound
+// next to their shared-memory / L1 traffic (profiles/r02_spmm_ring_ncu_summary.md), so their inner loops use these.
+struct F4p { unsigned long long lo, hi; };   // {x, y}, {z, w}
+__device__ __forceinline__ unsigned long long f2_pack(float a, float b) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ F4p f4_pack(float4 v) { F4p r; r.lo = f2_pack(v.x, v.y); r.hi = f2_pack(v.z, v.w); return r; }
+__device__ __forceinline__ float4 f4_unpack(const F4p& a) {
+  float4 v;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(v.x), "=f"(v.y) : "l"(a.lo));
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(v.z), "=f"(v.w) : "l"(a.hi));
+  return v;
+}
+// acc += w * (v - p), per component: sub then fma, exactly what `acc.x += w * (v.x - p.x)` compiles to
+__device__ __forceinline__ void f4_diff_fma(F4p& acc, float w, float4 v, const F4p& p) {
+  const unsigned long long ww = f2_pack(w, w);
+  unsigned long long d0, d1;
+  asm("sub.f32x2 %0, %1, %2;" : "=l"(d0) : "l"(f2_pack(v.x, v.y)), "l"(p.lo));
+  asm("sub.f32x2 %0, %1, %2;" : "=l"(d1) : "l"(f2_pack(v.z, v.w)), "l"(p.hi));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(acc.lo) : "l"(ww), "l"(d0), "l"(acc.lo));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(acc.hi) : "l"(ww), "l"(d1), "l"(acc.hi));
+}
+
 // ---- stage entry points shared between translation units ---------------------------------------------------
 int tcs_impl_scan_u32(tcs_ctx* ctx, const uint32_t* d_in, uint32_t* d_out, size_t n);  // exclusive sum, d_out[n] = total (n+1 outputs)
 int tcs_impl_read_u32(tcs_ctx* ctx, const uint32_t* d_ptr, uint32_t* out);             // synchronising scalar read

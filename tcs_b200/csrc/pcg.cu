@@ -87,23 +87,25 @@ __global__ void __launch_bounds__(256) k_spmm(int n, int Q, const uint32_t* __re
       const uint32_t a1 = rowptr[row + 1];
       const float4 p = P[(size_t)row * Q + q];
       const float d = gdiag[row];
-      float4 y = make_float4(d * p.x, d * p.y, d * p.z, d * p.w);
+      const F4p pp = f4_pack(p);
+      F4p yy = f4_pack(make_float4(d * p.x, d * p.y, d * p.z, d * p.w));
       for (; a + 4 <= a1; a += 4) {
         int c0 = col[a], c1 = col[a + 1], c2 = col[a + 2], c3 = col[a + 3];
         float w0 = val[a], w1 = val[a + 1], w2 = val[a + 2], w3 = val[a + 3];
         float4 t0 = P[(size_t)c0 * Q + q], t1 = P[(size_t)c1 * Q + q];
         float4 t2 = P[(size_t)c2 * Q + q], t3 = P[(size_t)c3 * Q + q];
-        y.x += w0 * (t0.x - p.x); y.y += w0 * (t0.y - p.y); y.z += w0 * (t0.z - p.z); y.w += w0 * (t0.w - p.w);
-        y.x += w1 * (t1.x - p.x); y.y += w1 * (t1.y - p.y); y.z += w1 * (t1.z - p.z); y.w += w1 * (t1.w - p.w);
-        y.x += w2 * (t2.x - p.x); y.y += w2 * (t2.y - p.y); y.z += w2 * (t2.z - p.z); y.w += w2 * (t2.w - p.w);
-        y.x += w3 * (t3.x - p.x); y.y += w3 * (t3.y - p.y); y.z += w3 * (t3.z - p.z); y.w += w3 * (t3.w - p.w);
+        f4_diff_fma(yy, w0, t0, pp);
+        f4_diff_fma(yy, w1, t1, pp);
+        f4_diff_fma(yy, w2, t2, pp);
+        f4_diff_fma(yy, w3, t3, pp);
       }
       for (; a < a1; ++a) {
         int c = col[a];
         float w = val[a];
         float4 t = P[(size_t)c * Q + q];
-        y.x += w * (t.x - p.x); y.y += w * (t.y - p.y); y.z += w * (t.z - p.z); y.w += w * (t.w - p.w);
+        f4_diff_fma(yy, w, t, pp);
       }
+      const float4 y = f4_unpack(yy);
       AP[(size_t)row * Q + q] = y;
       acc[0] += (double)p.x * (double)y.x; acc[1] += (double)p.y * (double)y.y;
       acc[2] += (double)p.z * (double)y.z; acc[3] += (double)p.w * (double)y.w;

@@ -200,14 +200,16 @@ __global__ void __launch_bounds__(256, 2)
         const uint32_t a1 = rp_s[lr + 1] - a_lo;
         const float4 p = *(const float4*)(Pq + (r0 + lr - w0) * rowbytes);
         const float d = diag_s[lr];
-        float4 y = make_float4(d * p.x, d * p.y, d * p.z, d * p.w);
+        const F4p pp = f4_pack(p);
+        F4p yy = f4_pack(make_float4(d * p.x, d * p.y, d * p.z, d * p.w));
 #pragma unroll 4
         for (; a < a1; ++a) {
           const int2 e = cv_s[a];
           const float w = __int_as_float(e.y);
           const float4 t = *(const float4*)(Pq + e.x);
-          y.x += w * (t.x - p.x); y.y += w * (t.y - p.y); y.z += w * (t.z - p.z); y.w += w * (t.w - p.w);
+          f4_diff_fma(yy, w, t, pp);
         }
+        const float4 y = f4_unpack(yy);
         AP[(size_t)(r0 + lr) * Q + q] = y;
         acc[0] += (double)p.x * (double)y.x; acc[1] += (double)p.y * (double)y.y;
         acc[2] += (double)p.z * (double)y.z; acc[3] += (double)p.w * (double)y.w;

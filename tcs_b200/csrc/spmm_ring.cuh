@@ -318,14 +318,16 @@ __global__ void __launch_bounds__(kRingThreads, 1)
         const int own = (own_by_parity && ((row ^ pos) & 1)) ? own_ring2 : T.off_ring;
         const float4 p = *(const float4*)(Pq + own + (row & mask) * pitch);
         const float d = ((const float*)(st + T.off_meta + kRingMetaHdr + 2 * T.R))[lr];
-        float4 y = make_float4(d * p.x, d * p.y, d * p.z, d * p.w);
+        const F4p pp = f4_pack(p);
+        F4p yy = f4_pack(make_float4(d * p.x, d * p.y, d * p.z, d * p.w));
 #pragma unroll 4
         for (int k = 0; k < L; ++k) {
           const uint32_t off = off_s[k * G];
           const float w = w_s[k * G];
           const float4 v = *(const float4*)(Pq + (off << 4));
-          y.x += w * (v.x - p.x); y.y += w * (v.y - p.y); y.z += w * (v.z - p.z); y.w += w * (v.w - p.w);
+          f4_diff_fma(yy, w, v, pp);   // y += w * (v - p): two FADD2 + two FFMA2
         }
+        const float4 y = f4_unpack(yy);
         if (row < n) {
           AP[(size_t)row * Q + q] = y;
           acc[0] += (double)p.x * (double)y.x; acc[1] += (double)p.y * (double)y.y;
