@@ -155,7 +155,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([c.strip() for c in out.strip().split(",")])
             except Exception:
                 pass
-            self._halt.wait(0.05 if self.nv is not None else 1.0)
+            self._halt.wait(0.2 if self.nv is not None else 1.0)
 
     def stop(self):
         self._halt.set()

@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(256) k_restrict(int nc, int Q, const uint32_t*
 //   SMOOTH = 0: out = rhs - y                       (residual of the pre-smoothed iterate)
 //   SMOOTH = 1: out = x + winvd * (rhs - y)         (post-smoothing; DOT: dots[c] += rhs . out per column, float64)
 template <int SMOOTH, int DOT>
-__global__ void __launch_bounds__(256) k_level_spmm(int n, int Q, const uint32_t* __restrict__ rowptr,
+__global__ void __launch_bounds__(256, 6) k_level_spmm(int n, int Q, const uint32_t* __restrict__ rowptr,
                                                     const int* __restrict__ col, const float* __restrict__ val,
                                                     const float* __restrict__ gdiag, const float* __restrict__ winvd,
                                                     const float4* __restrict__ X, const float4* __restrict__ RHS,
@@ -601,10 +601,12 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Hierarchy& H) {
   return TCS_OK;
 }
 
+// grid of the grid-stride level kernels: exactly the resident CTAs (6 per SM, see the launch bounds of k_level_spmm)
+constexpr unsigned kLevelCtasPerSm = 6;
 inline unsigned spmm_grid(tcs_ctx* ctx, int n, int Q) {
   const int rows_per_block = 256 / Q;
   const unsigned need = (unsigned)((n + rows_per_block - 1) / rows_per_block);
-  return std::max(1u, std::min(need, (unsigned)ctx->sm_count * 8u));
+  return std::max(1u, std::min(need, (unsigned)ctx->sm_count * kLevelCtasPerSm));
 }
 
 // One V(1,1) cycle on levels >= 1 for the fine residual R (n x 4Q): afterwards result(H) holds e_1 (the coarse

@@ -737,7 +737,21 @@ namespace {
 struct PcgLaunch {
   unsigned grid, block;
   size_t smem;
+  // grid-stride kernels with their own register budgets: exactly the resident CTAs (a grid of 8 CTAs per SM leaves a
+  // 78-register kernel with 2.67 waves: the last one runs a third empty)
+  unsigned grid_update, grid_dir;
 };
+
+// resident CTAs of `fn` on the whole device, capped by the CTAs the rows need
+template <typename F>
+unsigned resident_grid(tcs_ctx* ctx, F fn, int block, size_t smem, unsigned need, unsigned fallback_per_sm) {
+  int nb = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, block, smem) != cudaSuccess || nb < 1) {
+    cudaGetLastError();
+    nb = (int)fallback_per_sm;
+  }
+  return std::max(1u, std::min(need, (unsigned)ctx->sm_count * (unsigned)nb));
+}
 
 __global__ void k_tile_max_nnz(int n, int R, const uint32_t* __restrict__ rowptr, uint32_t* __restrict__ out) {
   int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1009,7 +1023,7 @@ int spmm_plan_ring(tcs_ctx* ctx, tcs_system& S) {
   return TCS_OK;
 }
 
-PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q);
+PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q, bool vector_kernels = true);
 
 // AP = L P, pAp += p . Ap per column
 void launch_spmm(tcs_ctx* ctx, tcs_system& S, const float4* P4, float4* AP4, double* pAp) {
@@ -1025,12 +1039,12 @@ void launch_spmm(tcs_ctx* ctx, tcs_system& S, const float4* P4, float4* AP4, dou
     LAUNCH(ctx, k_spmm_tiled, grid, 256, (size_t)T.total, n, Q, T, S.rowptr.p, S.cv.p, S.far_rows.p, S.tile_far_ptr.p,
            S.gdiag.p, P4, AP4, pAp);
   } else {
-    const PcgLaunch L = pcg_launch_shape(ctx, n, Q);
+    const PcgLaunch L = pcg_launch_shape(ctx, n, Q, false);
     LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.gdiag.p, P4, AP4, pAp);
   }
 }
 
-PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q) {
+PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q, bool vector_kernels) {
   PcgLaunch L;
   L.block = 256;
   const int rows_per_block = 256 / Q;
@@ -1038,6 +1052,11 @@ PcgLaunch pcg_launch_shape(tcs_ctx* ctx, int n, int Q) {
   // persistent-style grid: a multiple of the SM count, 8 resident CTAs of 256 threads per SM
   L.grid = std::max(1u, std::min(need, (unsigned)ctx->sm_count * 8u));
   L.smem = (size_t)4 * Q * sizeof(double);
+  L.grid_update = L.grid_dir = L.grid;
+  if (vector_kernels) {   // two occupancy queries: once per solve, not per launch
+    L.grid_update = resident_grid(ctx, k_pcg_update, 256, L.smem, need, 4);
+    L.grid_dir = resident_grid(ctx, k_pcg_dir, 256, 0, need, 3);
+  }
   return L;
 }
 
@@ -1370,10 +1389,10 @@ int tcs_impl_pcg_solve(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts
       launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp0);
       if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
       ++spmm_launches;
-      LAUNCH(ctx, k_pcg_update, L.grid, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
+      LAUNCH(ctx, k_pcg_update, L.grid_update, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
              d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr, AH.on ? d_rr3 + s1 * Kp0 : (double*)nullptr);
       if (AH.on) TRY(amg::apply(ctx, AH, Qw, R4, d_rz + s1 * Kp0));
-      LAUNCH(ctx, k_pcg_dir, L.grid, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
+      LAUNCH(ctx, k_pcg_dir, L.grid_dir, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
              d_pAp + s0 * Kp0, d_rz + s1 * Kp0, d_pAp + s1 * Kp0, d_rz + s2 * Kp0,
              AH.on ? d_rr3 + s2 * Kp0 : (double*)nullptr, frozen.p, d_rz0, done_factor, pr,
              AH.on ? amg::fine_agg(AH) : (const uint32_t*)nullptr, AH.on ? amg::result(AH) : (const float4*)nullptr,
