@@ -22,7 +22,7 @@ for variant in sys.argv[2:] or [""]:
     os.environ.update(kv)
     best = None
     for rep in range(2):
-        r = ctx.segment_cloud(res, sx, sl, preset=0, mode=capi.MODE_FAST)
+        r = ctx.segment_cloud(res, sx, sl, preset=0, mode=capi.MODE_PARITY if os.environ.get('TCS_SWEEP_MODE') == 'parity' else capi.MODE_FAST)
         info = r["info"].as_dict()
         if best is None or info["solve_ms"] < best["solve_ms"]:
             best = info

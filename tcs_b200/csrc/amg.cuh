@@ -512,7 +512,15 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Hierarchy& H) {
   CK(cudaEventRecord(e0, ctx->stream));
   const float w = (float)env_double("TCS_AMG_OMEGA", 0.9);
   const int rounds = env_i("TCS_AMG_ROUNDS", 2);
-  const int passes = std::max(1, env_i("TCS_AMG_PASSES", 2));
+  const int passes = std::max(1, env_i("TCS_AMG_PASSES", 1));
+  // TCS_AMG_SCHEDULE = "p0:p1:..." (or commas): pairwise passes of level 0 -> 1, 1 -> 2, ... (the last entry repeats)
+  std::vector<int> schedule;
+  if (const char* sc = getenv("TCS_AMG_SCHEDULE"))
+    for (const char* c = sc; *c;) {
+      schedule.push_back(std::max(1, atoi(c)));
+      while (*c && *c != ',' && *c != ':') ++c;
+      if (*c) ++c;
+    }
   H.over = (float)env_double("TCS_AMG_OVER", 1.3);
   Level& L0 = H.L[0];
   L0.A.n = n; L0.A.nnz = S.nnz_off; L0.A.rowptr = S.rowptr.p; L0.A.col = S.col.p; L0.A.val = S.val.p; L0.A.diag = S.diag.p;
@@ -527,7 +535,8 @@ inline int setup(tcs_ctx* ctx, tcs_system& S, int Kp0, Hierarchy& H) {
     Csr cur = F.A;
     const double* gcur = F.g.p;
     int np = 0;
-    for (; np < std::min(passes, 4); ++np) {
+    const int level_passes = schedule.empty() ? passes : schedule[std::min((size_t)lev, schedule.size() - 1)];
+    for (; np < std::min(level_passes, 4); ++np) {
       TRY(coarsen_pass(ctx, cur, gcur, w, rounds, P[np]));
       if (np == 0) total.swap(P[0].agg);
       else {
@@ -609,6 +618,14 @@ inline unsigned spmm_grid(tcs_ctx* ctx, int n, int Q) {
   return std::max(1u, std::min(need, (unsigned)ctx->sm_count * kLevelCtasPerSm));
 }
 
+template <int SMOOTH, int DOT>
+inline void launch_level_spmm(tcs_ctx* ctx, const Level& C, int Q, const float4* X, const float4* RHS, float4* OUT,
+                              double* dots) {
+  const size_t dsm = (size_t)4 * Q * sizeof(double);
+  LAUNCH(ctx, (k_level_spmm<SMOOTH, DOT>), spmm_grid(ctx, C.A.n, Q), 256, dsm, C.A.n, Q, C.A.rowptr, C.A.col, C.A.val,
+           C.gdiag.p, C.winvd.p, X, RHS, OUT, dots);
+}
+
 // One V(1,1) cycle on levels >= 1 for the fine residual R (n x 4Q): afterwards result(H) holds e_1 (the coarse
 // correction at level 1, to be prolonged by the caller as p += Z0 e_1) and rz_target[c] += r_1 . e_1 per column.
 inline int apply(tcs_ctx* ctx, Hierarchy& H, int Q, const float4* R4, double* rz_target) {
@@ -623,8 +640,7 @@ inline int apply(tcs_ctx* ctx, Hierarchy& H, int Q, const float4* R4, double* rz
     LAUNCH(ctx, k_restrict, div_up((size_t)C.A.n * Q, 256), 256, 0, C.A.n, Q, F.cptr.p, F.cidx.p, src, C.winvd.p,
            (float4*)C.r.p, bottom && H.dense ? (float4*)nullptr : (float4*)C.x.p);
     if (bottom) break;
-    LAUNCH(ctx, (k_level_spmm<0, 0>), spmm_grid(ctx, C.A.n, Q), 256, dsm, C.A.n, Q, C.A.rowptr, C.A.col, C.A.val, C.gdiag.p,
-           C.winvd.p, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, (double*)nullptr);
+    launch_level_spmm<0, 0>(ctx, C, Q, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, nullptr);
   }
   // bottom
   {
@@ -633,8 +649,7 @@ inline int apply(tcs_ctx* ctx, Hierarchy& H, int Q, const float4* R4, double* rz
       LAUNCH(ctx, k_dense_apply, (unsigned)H.m, 128, 0, H.m, Q, H.Einv.p, (const float4*)B.r.p, (float4*)B.t.p);
     } else {
       // no dense inverse (many collapsed components): the smoother is exact on rows without off-diagonal entries
-      LAUNCH(ctx, (k_level_spmm<1, 0>), spmm_grid(ctx, B.A.n, Q), 256, dsm, B.A.n, Q, B.A.rowptr, B.A.col, B.A.val, B.gdiag.p,
-             B.winvd.p, (const float4*)B.x.p, (const float4*)B.r.p, (float4*)B.t.p, (double*)nullptr);
+      launch_level_spmm<1, 0>(ctx, B, Q, (const float4*)B.x.p, (const float4*)B.r.p, (float4*)B.t.p, nullptr);
     }
     if (last == 1)
       LAUNCH(ctx, k_dot, std::min(spmm_grid(ctx, B.A.n, Q), 64u), 256, dsm, B.A.n, Q, (const float4*)B.r.p, (const float4*)B.t.p, rz_target);
@@ -645,11 +660,9 @@ inline int apply(tcs_ctx* ctx, Hierarchy& H, int Q, const float4* R4, double* rz
     Level& N = H.L[l + 1];
     LAUNCH(ctx, k_prolong, div_up((size_t)C.A.n * Q, 256), 256, 0, C.A.n, Q, H.over, C.agg.p, (const float4*)N.t.p, (float4*)C.x.p);
     if (l == 1)
-      LAUNCH(ctx, (k_level_spmm<1, 1>), spmm_grid(ctx, C.A.n, Q), 256, dsm, C.A.n, Q, C.A.rowptr, C.A.col, C.A.val, C.gdiag.p,
-             C.winvd.p, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, rz_target);
+      launch_level_spmm<1, 1>(ctx, C, Q, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, rz_target);
     else
-      LAUNCH(ctx, (k_level_spmm<1, 0>), spmm_grid(ctx, C.A.n, Q), 256, dsm, C.A.n, Q, C.A.rowptr, C.A.col, C.A.val, C.gdiag.p,
-             C.winvd.p, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, (double*)nullptr);
+      launch_level_spmm<1, 0>(ctx, C, Q, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, nullptr);
   }
   return TCS_OK;
 }

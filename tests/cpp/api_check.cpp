@@ -4,6 +4,7 @@
 //                 same names (builder, normals, smoothen, normals, signs, EdgeWeightComputer, setInputGraph, segment)
 // in.bin : u64 n, f32 xyz[3n], u32 rgba[n], u64 ns, f32 seed_xyz[3ns], u32 seed_label[ns]
 // out.bin: i32 cluster_of_point_or_vertex[m], u64 V, u32 vertex_colour[V], u64 K, f32 potentials[V*K] (col-major)
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -49,7 +50,11 @@ int main(int argc, char** argv) {
   }
 
   std::vector<pcl::PointIndices> clusters;
-  RWS rws(true);
+  // TCS_API_POTENTIALS=0: do not keep the potentials (the reference's default); TCS_API_REPEAT=n: time n further
+  // segment() calls of the class path on fresh objects (profiles/: e2e through the C++ class)
+  const bool keep_potentials = !std::getenv("TCS_API_POTENTIALS") || std::atoi(std::getenv("TCS_API_POTENTIALS")) != 0;
+  const int repeat = std::getenv("TCS_API_REPEAT") ? std::atoi(std::getenv("TCS_API_REPEAT")) : 0;
+  RWS rws(keep_potentials);
   size_t m = n;
   try {
     if (mode == "class") {
@@ -57,6 +62,22 @@ int main(int argc, char** argv) {
       rws.setInputCloud(cloud);
       rws.setSeeds(seeds);
       rws.segment(clusters);
+      double best = 1e300, sum = 0.0;
+      for (int r = 0; r < repeat; ++r) {
+        std::vector<pcl::PointIndices> again;
+        const std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+        RWS timed(keep_potentials);
+        timed.setVoxelResolution(resolution);
+        timed.setInputCloud(cloud);
+        timed.setSeeds(seeds);
+        timed.segment(again);
+        const double ms = 1e3 * std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        best = ms < best ? ms : best;
+        sum += ms;
+      }
+      if (repeat > 0)
+        std::printf("api_check class timing: %d x (construct + setInputCloud + setSeeds + segment(clusters)), host cloud in, clusters on the "
+                    "host out: best %.2f ms, mean %.2f ms, potentials %s\n", repeat, best, sum / repeat, keep_potentials ? "kept" : "not kept");
     } else {
       using namespace pcl::graph;
       typedef RWS::Graph Graph;
