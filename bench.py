@@ -246,7 +246,7 @@ def workload_config(args, world):
     if args.config == "c5":
         return {"workload": "C5: %d synthetic 640x480 RGB-D scenes (%d distinct, cycled; ~47 k vertices each), %g m voxels, "
                             "8 labels x %d seeds, class weight preset, FAST mode, PCG tol 1e-6; scenes round-robin over the "
-                            "ranks, batches of %d through tcs_segment_batch" % (args.scenes, args.distinct, C5_RES, C5_SEEDS, args.batch),
+                            "ranks, batches of at most %d through tcs_segment_batch" % (args.scenes, args.distinct, C5_RES, C5_SEEDS, args.batch),
                 "scenes_per_step": args.scenes,
                 "l2": "a batch's merged system (1.5 M rows x 8 columns: vectors 48 MB each, matrix 170 MB, hierarchy) exceeds L2"}
     w, h = (1280, 960) if args.small else (C4_W, C4_H)
@@ -550,7 +550,11 @@ def run_c5(args, rank, local_rank, world):
     host = {k: _pinned_records(torch, data[k][0], data[k][1]) for k in distinct}
     dev = {k: host[k].to("cuda", non_blocking=False) for k in distinct}
     seeds = {k: (np.ascontiguousarray(data[k][2], np.float32), np.ascontiguousarray(data[k][3], np.uint32)) for k in distinct}
+    # batches of at most --batch scenes, sized so that every worker context gets the same number of batches (128 scenes
+    # on 3 contexts: 6 batches of 21-22 instead of 4 of 32, which would leave two contexts idle in the second round)
     B = max(1, args.batch)
+    rounds = max(1, -(-len(mine) // (W * B)))
+    B = max(1, min(B, -(-len(mine) // (W * rounds))))
     pc_host = [torch.empty((B, n), dtype=torch.int32).pin_memory() for _ in range(W)]
     vc_host = [torch.empty((B, n), dtype=torch.int32).pin_memory() for _ in range(W)]
     opts = capi.default_opts(time_spmm=0)
@@ -658,7 +662,7 @@ def run_c5(args, rank, local_rank, world):
                            scenes_per_s=scenes_all * args.steps / (ms_max * 1e-3),
                            scenes_per_s_e2e=scenes_all * args.steps / (ms_e2e_max * 1e-3),
                            vertices_per_scene=int(V // args.steps // max(1, len(mine))), batch_rows=nrows, batch_nnz=nnz, labels=K,
-                           contexts_per_gpu=W, pcg_iterations_per_batch_rank0=its, converged=all(i["converged"] for i in infos),
+                           contexts_per_gpu=W, scenes_per_batch_rank0=B, pcg_iterations_per_batch_rank0=its, converged=all(i["converged"] for i in infos),
                            max_rel_residual=max(max(i["rel_residual"]) for i in infos),
                            preconditioner="Jacobi + V(1,1) cycle on a device-built aggregation hierarchy of the merged "
                                           "block-diagonal system; one CG recurrence per (scene, column)"),

@@ -102,6 +102,11 @@ int tcs_ctx_create(int device, tcs_ctx** out);
 int tcs_ctx_create_on_stream(int device, void* cuda_stream, tcs_ctx** out);
 void tcs_ctx_destroy(tcs_ctx* ctx);
 const char* tcs_last_error(const tcs_ctx* ctx);
+/* Page-locked ("pinned") host memory, usable with every device of the process; NULL on failure.  No counterpart in the
+ * reference (a CPU library).  Host buffers passed to tcs_cloud_upload / tcs_segment_batch are copied at full PCIe speed,
+ * asynchronously, only when they are pinned; pageable buffers work but go through the driver's staging copy. */
+void* tcs_host_alloc(size_t bytes);
+void tcs_host_free(void* p);
 int tcs_ctx_synchronize(tcs_ctx* ctx);
 void* tcs_ctx_stream(tcs_ctx* ctx);
 /* number of kernels launched by this library on this context since creation (bench.py's gpu_launches) */

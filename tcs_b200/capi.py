@@ -40,7 +40,7 @@ EXPORTS = [
     "tcs_components", "tcs_solver_opts_default", "tcs_nearest_vertices", "tcs_random_walker", "tcs_segment_cloud",
     "tcs_graph_download_potentials", "tcs_graph_download_colours", "tcs_graph_d_colours",
     "tcs_graph_d_point_cluster", "tcs_bench_spmm", "tcs_check_spmm", "tcs_graph_download_best",
-    "tcs_graph_d_best_potential", "tcs_build_nn_graph", "tcs_segment_batch", "tcs_nearest_vertices_noalloc", "tcs_edge_weights_ex",
+    "tcs_graph_d_best_potential", "tcs_host_alloc", "tcs_host_free", "tcs_build_nn_graph", "tcs_segment_batch", "tcs_nearest_vertices_noalloc", "tcs_edge_weights_ex",
 ]
 
 

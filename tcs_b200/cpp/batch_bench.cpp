@@ -12,9 +12,29 @@
 
 #include "tcs/batch_segmenter.h"
 
+// scene buffers live in pinned host memory (tcs_host_alloc): the copies to the GPUs run at PCIe speed
+template <typename T>
+struct PinnedArray {
+  T* p = nullptr;
+  size_t n = 0;
+  bool resize(size_t count) {
+    tcs_host_free(p);
+    n = count;
+    p = count ? (T*)tcs_host_alloc(count * sizeof(T)) : nullptr;
+    return count == 0 || p != nullptr;
+  }
+  T* data() const { return p; }
+  size_t size() const { return n; }
+  ~PinnedArray() { tcs_host_free(p); }
+  PinnedArray() {}
+  PinnedArray(const PinnedArray&) = delete;
+  PinnedArray& operator=(const PinnedArray&) = delete;
+};
 struct Scene {
-  std::vector<float> xyz, seed_xyz;
-  std::vector<uint32_t> rgba, seed_label;
+  PinnedArray<float> xyz;
+  PinnedArray<uint32_t> rgba;
+  std::vector<float> seed_xyz;
+  std::vector<uint32_t> seed_label;
 };
 
 static bool read_exact(FILE* f, void* p, size_t bytes) { return bytes == 0 || std::fread(p, 1, bytes, f) == bytes; }
@@ -43,11 +63,13 @@ int main(int argc, char** argv) {
   uint64_t count = 0;
   if (!read_exact(f, &count, 8) || count == 0 || count > (1u << 20)) { std::fprintf(stderr, "tcs_batch_bench: bad scene file\n"); return 2; }
   std::vector<Scene> file_scenes((size_t)count);
+  bool pinned_ok = true;
   for (size_t s = 0; s < file_scenes.size(); ++s) {
     uint64_t n = 0, ns = 0;
     Scene& sc = file_scenes[s];
     if (!read_exact(f, &n, 8) || n > (1ull << 31)) { std::fprintf(stderr, "tcs_batch_bench: bad scene %zu\n", s); return 2; }
-    sc.xyz.resize(3 * n); sc.rgba.resize(n);
+    pinned_ok = sc.xyz.resize(3 * n) && sc.rgba.resize(n);
+    if (!pinned_ok) { std::fprintf(stderr, "tcs_batch_bench: tcs::BatchSegmenter needs a CUDA device (no CPU fallback): pinned host allocation failed\n"); return 3; }
     if (!read_exact(f, sc.xyz.data(), 12 * n) || !read_exact(f, sc.rgba.data(), 4 * n) || !read_exact(f, &ns, 8) || ns > (1u << 20)) {
       std::fprintf(stderr, "tcs_batch_bench: short scene %zu\n", s); return 2;
     }

@@ -66,6 +66,17 @@ extern "C" void tcs_ctx_destroy(tcs_ctx* ctx) {
   delete ctx;
 }
 
+// page-locked host memory usable from every device of the process: host buffers handed to the library are copied at
+// full PCIe speed and asynchronously only when they are pinned (pageable memory goes through the driver's staging copy)
+extern "C" void* tcs_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+extern "C" void tcs_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
 extern "C" const char* tcs_last_error(const tcs_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 extern "C" void* tcs_ctx_stream(tcs_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 extern "C" long long tcs_ctx_launch_count(const tcs_ctx* ctx) { return ctx ? ctx->launches : 0; }
