@@ -100,10 +100,14 @@ class BatchSegmenter {
         const size_t d = w / (size_t)per_device_;
         std::vector<tcs_scene> arr;
         Pinned& pin = pinned_[w];
+        // batches of at most batch_ scenes, sized so that the GPU's workers all get the same number of batches
+        const size_t nd = mine[d].size(), per_round = (size_t)per_device_ * (size_t)batch_;
+        const size_t rounds = nd ? (nd + per_round - 1) / per_round : 1;
+        const size_t step = nd ? (nd + (size_t)per_device_ * rounds - 1) / ((size_t)per_device_ * rounds) : 1;
         while (errors[w].empty()) {
-          const size_t b0 = cursor[d].fetch_add((size_t)batch_);
-          if (b0 >= mine[d].size()) break;
-          const size_t b1 = b0 + (size_t)batch_ < mine[d].size() ? b0 + (size_t)batch_ : mine[d].size();
+          const size_t b0 = cursor[d].fetch_add(step);
+          if (b0 >= nd) break;
+          const size_t b1 = b0 + step < nd ? b0 + step : nd;
           arr.assign(b1 - b0, tcs_scene());
           size_t words = 0;   // pinned staging of this batch's outputs: [point clusters][vertex colours] per scene
           for (size_t k = b0; k < b1; ++k) words += scenes[mine[d][k]].n * (want_point_clusters_ ? 2 : 1);

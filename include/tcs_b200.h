@@ -87,7 +87,8 @@ typedef struct tcs_solve_info {
   int ncomponents;
   long long near_ties;          /* vertices whose two largest potentials differ by < 1e-6 */
   double rel_residual[TCS_MAX_LABELS]; /* float64 true residual per colour column */
-  float spmm_ms;                /* device time summed over all SpMM launches (CUDA events, ctx stream) */
+  float spmm_ms;                /* SAMPLED: mean device time of the first <= 64 (batched solve: 32) SpMM launches of the
+                                   solve (one CUDA event pair each, ctx stream) x spmm_launches; 0 unless time_spmm */
   int spmm_launches;
   float solve_ms;               /* device time of the whole PCG loop */
   float stage_ms[12];           /* build, normals, smoothen, normals2, signs, weights, components, seeds,
