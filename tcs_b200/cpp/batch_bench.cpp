@@ -44,7 +44,7 @@ int main(int argc, char** argv) {
     std::fprintf(stderr, "usage: tcs_batch_bench scenes.bin [--gpus G] [--batch B] [--contexts C] [--repeat R] [--total N] [--fast] [--labels out.bin]\n");
     return 2;
   }
-  int gpus = 1, batch = 32, contexts = 2, repeat = 3, fast = 0;
+  int gpus = 1, batch = 32, contexts = 2, repeat = 3, fast = 0, clusters = 1, replicate = 0;
   size_t total = 0;
   std::string labels_path;
   for (int i = 2; i < argc; ++i) {
@@ -55,6 +55,8 @@ int main(int argc, char** argv) {
     else if (a == "--repeat" && i + 1 < argc) repeat = std::atoi(argv[++i]);
     else if (a == "--total" && i + 1 < argc) total = (size_t)std::atoll(argv[++i]);
     else if (a == "--fast") fast = 1;
+    else if (a == "--no-clusters") clusters = 0;     // vertex colours only (no per-point cluster array)
+    else if (a == "--replicate") replicate = 1;      // every GPU reads its own pinned copy of the scene file
     else if (a == "--labels" && i + 1 < argc) labels_path = argv[++i];
     else { std::fprintf(stderr, "tcs_batch_bench: unknown option %s\n", a.c_str()); return 2; }
   }
@@ -80,9 +82,26 @@ int main(int argc, char** argv) {
   }
   std::fclose(f);
   if (total == 0) total = file_scenes.size();
+  // --replicate: one pinned copy of the scenes per GPU (scene i of the job runs on GPU i mod G)
+  std::vector<std::vector<Scene> > copies;
+  if (replicate && gpus > 1) {
+    copies.resize((size_t)gpus - 1);
+    for (size_t c = 0; c < copies.size(); ++c) {
+      copies[c] = std::vector<Scene>(file_scenes.size());
+      for (size_t k = 0; k < file_scenes.size(); ++k) {
+        Scene& d = copies[c][k];
+        const Scene& o = file_scenes[k];
+        if (!d.xyz.resize(o.xyz.size()) || !d.rgba.resize(o.rgba.size())) { std::fprintf(stderr, "tcs_batch_bench: pinned allocation failed\n"); return 3; }
+        std::memcpy(d.xyz.data(), o.xyz.data(), o.xyz.size() * 4);
+        std::memcpy(d.rgba.data(), o.rgba.data(), o.rgba.size() * 4);
+        d.seed_xyz = o.seed_xyz; d.seed_label = o.seed_label;
+      }
+    }
+  }
   std::vector<tcs::SceneInput> job(total);
   for (size_t i = 0; i < total; ++i) {
-    const Scene& sc = file_scenes[i % file_scenes.size()];
+    const size_t dev = i % (size_t)gpus;
+    const Scene& sc = (dev > 0 && !copies.empty()) ? copies[dev - 1][i % file_scenes.size()] : file_scenes[i % file_scenes.size()];
     tcs::SceneInput& in = job[i];
     in.xyz = sc.xyz.data(); in.xyz_stride = 12; in.rgba = sc.rgba.data(); in.rgba_stride = 4; in.n = sc.rgba.size();
     in.seed_xyz = sc.seed_xyz.data(); in.seed_label = sc.seed_label.data(); in.ns = sc.seed_label.size();
@@ -93,10 +112,11 @@ int main(int argc, char** argv) {
     tcs::BatchSegmenter seg(devices, batch, contexts);
     seg.setVoxelResolution(0.006f);
     seg.setArithmeticMode(fast ? TCS_MODE_FAST : TCS_MODE_PARITY);
+    seg.setWantPointClusters(clusters != 0);
     std::vector<tcs::SceneResult> res;
     double best = 1e300;
     for (int r = 0; r < repeat + 1; ++r) {            // the first run warms allocators, module loading and the pools
-      res = seg.segment(job);
+      seg.segment(job, res);                         // reuses the result vectors of the previous run
       if (r > 0 && seg.lastSeconds() < best) best = seg.lastSeconds();
     }
     if (repeat < 1) best = seg.lastSeconds();

@@ -238,23 +238,60 @@ int pcg_solve_batched(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts&
     evs.resize(2 * kMaxSamples);
     for (auto& e : evs) CK(cudaEventCreate(&e));
   }
+  // One iteration = ~55 launches, all with the same arguments every time except the ping-pong of the two r.z
+  // accumulators.  A chunk of `probe` iterations is therefore captured ONCE per solve into a CUDA graph and replayed:
+  // one cudaGraphLaunch per chunk instead of ~220 kernel launches (a single host process drives at most ~430 k
+  // launches/s - with 24 worker threads on 8 GPUs that was the limit of tcs::BatchSegmenter - and dependent small
+  // kernels start back to back on the device).  TCS_GRAPH=0 or SpMM timing (events cannot be read back from a
+  // capture) select the launch-by-launch path.
+  auto enqueue_iteration = [&](int c, bool timed) -> int {
+    if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
+    launch_spmm(ctx, S, P4, AP4, d_dummy);
+    if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
+    LAUNCH(ctx, batch::k_dot, grid, 256, dsm, Q, Kp, d_rb.p, (const float4*)P4, (const float4*)AP4, d_pAp);
+    LAUNCH(ctx, batch::k_alpha, div_up(count, 128), 128, 0, count, d_rz[c], d_pAp, d_rz0, frozen.p, done_factor, d_al,
+           d_rz[c ^ 1], d_rr);
+    LAUNCH(ctx, batch::k_update, grid, 256, 0, Q, Kp, d_rb.p, d_al, (const float4*)AP4, R4);
+    TRY(amg::apply(ctx, AH, Q, R4, d_dummy));
+    LAUNCH(ctx, batch::k_dot_rz, grid, 256, dsm, Q, Kp, d_rb.p, R4, invd.p, agg, e1, d_rz[c ^ 1], d_rr);
+    LAUNCH(ctx, batch::k_beta, div_up(count, 128), 128, 0, count, d_rz[c], d_rz[c ^ 1], d_rz0, frozen.p, done_factor, d_be,
+           d_pAp);
+    LAUNCH(ctx, batch::k_dir, grid, 256, 0, Q, Kp, d_rb.p, d_al, d_be, R4, P4, X.p, invd.p, agg, e1);
+    return TCS_OK;
+  };
+  struct ChunkGraph {
+    cudaGraphExec_t exec[2] = {nullptr, nullptr};   // by the parity of `cur` at the start of the chunk
+    long long nodes = 0;
+    ~ChunkGraph() { for (auto e : exec) if (e) cudaGraphExecDestroy(e); }
+  } cg;
+  const bool use_graph = !opts.time_spmm && env_int("TCS_GRAPH", 1) != 0;
   while (!converged && it < opts.max_iterations) {
     const int chunk = std::min(probe, opts.max_iterations - it);
+    if (use_graph && chunk == probe) {
+      if (!cg.exec[cur]) {
+        const long long before = ctx->launches;
+        CK(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+        int st = TCS_OK, c = cur;
+        for (int j = 0; j < chunk && st == TCS_OK; ++j, c ^= 1) st = enqueue_iteration(c, false);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+        cg.nodes = ctx->launches - before;
+        ctx->launches = before;                       // nothing ran yet: replays are counted below
+        if (st != TCS_OK) { if (graph) cudaGraphDestroy(graph); return st; }
+        CK(ce);
+        const cudaError_t ie = cudaGraphInstantiate(&cg.exec[cur], graph, 0);
+        cudaGraphDestroy(graph);
+        CK(ie);
+      }
+      CK(cudaGraphLaunch(cg.exec[cur], ctx->stream));
+      ctx->launches += cg.nodes;
+      it += chunk;
+      spmm_launches += chunk;
+      if (chunk & 1) cur ^= 1;
+    } else
     for (int j = 0; j < chunk; ++j, ++it) {
-      const bool timed = opts.time_spmm && samples < kMaxSamples;
-      if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
-      launch_spmm(ctx, S, P4, AP4, d_dummy);
-      if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
+      TRY(enqueue_iteration(cur, opts.time_spmm && samples < kMaxSamples));
       ++spmm_launches;
-      LAUNCH(ctx, batch::k_dot, grid, 256, dsm, Q, Kp, d_rb.p, (const float4*)P4, (const float4*)AP4, d_pAp);
-      LAUNCH(ctx, batch::k_alpha, div_up(count, 128), 128, 0, count, d_rz[cur], d_pAp, d_rz0, frozen.p, done_factor, d_al,
-             d_rz[cur ^ 1], d_rr);
-      LAUNCH(ctx, batch::k_update, grid, 256, 0, Q, Kp, d_rb.p, d_al, (const float4*)AP4, R4);
-      TRY(amg::apply(ctx, AH, Q, R4, d_dummy));
-      LAUNCH(ctx, batch::k_dot_rz, grid, 256, dsm, Q, Kp, d_rb.p, R4, invd.p, agg, e1, d_rz[cur ^ 1], d_rr);
-      LAUNCH(ctx, batch::k_beta, div_up(count, 128), 128, 0, count, d_rz[cur], d_rz[cur ^ 1], d_rz0, frozen.p, done_factor, d_be,
-             d_pAp);
-      LAUNCH(ctx, batch::k_dir, grid, 256, 0, Q, Kp, d_rb.p, d_al, d_be, R4, P4, X.p, invd.p, agg, e1);
       cur ^= 1;
     }
     // probe: recurrence ||r||^2 per (scene, column)

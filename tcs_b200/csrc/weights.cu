@@ -75,20 +75,58 @@ __global__ void k_edge_raw(size_t E, const uint32_t* __restrict__ esrc, const ui
     if (ts.norm[t] != TCS_NORM_NONE) raw[(size_t)ts.slot[t] * E + e] = term_distance(g, ts.kind[t], v1, v2);
 }
 
-// GloballyNormalizedTerm: total_weight_ is one float accumulator over the edges in order (PARITY).  One warp
-// stages 32 values per step with a coalesced load; lane 0 adds them in order.
-__global__ void k_sum_sequential(const float* __restrict__ d, size_t E, float* __restrict__ out) {
-  const int lane = threadIdx.x;
+// GloballyNormalizedTerm: total_weight_ is one float accumulator over the edges in order (PARITY) - a dependent chain
+// of float additions, whose floor is the FADD latency (~4 cycles per edge).  The chain must not wait for memory: all 256
+// threads stream the values into shared memory one chunk ahead (coalesced, double-buffered) and thread 0 adds the
+// current chunk from shared memory with 16-byte loads that do not depend on the sum.  (One warp loading 32 values per
+// step and adding them through shuffles spent 15 ns per edge waiting for its own global load.)
+constexpr int kSumChunk = 4096;
+__global__ void __launch_bounds__(256) k_sum_sequential(const float* __restrict__ d, size_t E, float* __restrict__ out) {
+  __shared__ __align__(16) float buf[2][kSumChunk];
+  constexpr int kPer = kSumChunk / 256;
   float total = 0.0f;
-  for (size_t base = 0; base < E; base += 32) {
-    float v = (base + lane < E) ? d[base + lane] : 0.0f;
-    int cnt = (int)min((size_t)32, E - base);
-    for (int k = 0; k < cnt; ++k) {
-      float vk = __shfl_sync(0xFFFFFFFFu, v, k);
-      total += vk;
-    }
+  for (int j = 0; j < kPer; ++j) {
+    const size_t e = (size_t)j * 256 + threadIdx.x;
+    buf[0][j * 256 + threadIdx.x] = e < E ? d[e] : 0.0f;
   }
-  if (lane == 0) *out = total;
+  __syncthreads();
+  const size_t chunks = (E + kSumChunk - 1) / kSumChunk;
+  for (size_t c = 0; c < chunks; ++c) {
+    float r[kPer];
+    const size_t next = (c + 1) * kSumChunk;
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) {   // next chunk -> registers (in flight while thread 0 adds)
+      const size_t e = next + (size_t)j * 256 + threadIdx.x;
+      r[j] = e < E ? d[e] : 0.0f;
+    }
+    if (threadIdx.x == 0) {
+      const float* b = buf[c & 1];
+      const int cnt = (int)min((size_t)kSumChunk, E - c * kSumChunk);
+      int k = 0;
+      if (cnt >= 16) {   // sixteen values ahead in registers: the shared-memory latency stays off the chain
+        const float4* b4 = (const float4*)b;
+        float4 a0 = b4[0], a1 = b4[1], a2 = b4[2], a3 = b4[3];
+        for (; k + 32 <= cnt; k += 16) {
+          const float4 n0 = b4[k / 4 + 4], n1 = b4[k / 4 + 5], n2 = b4[k / 4 + 6], n3 = b4[k / 4 + 7];
+          total += a0.x; total += a0.y; total += a0.z; total += a0.w;
+          total += a1.x; total += a1.y; total += a1.z; total += a1.w;
+          total += a2.x; total += a2.y; total += a2.z; total += a2.w;
+          total += a3.x; total += a3.y; total += a3.z; total += a3.w;
+          a0 = n0; a1 = n1; a2 = n2; a3 = n3;
+        }
+        total += a0.x; total += a0.y; total += a0.z; total += a0.w;
+        total += a1.x; total += a1.y; total += a1.z; total += a1.w;
+        total += a2.x; total += a2.y; total += a2.z; total += a2.w;
+        total += a3.x; total += a3.y; total += a3.z; total += a3.w;
+        k += 16;
+      }
+      for (; k < cnt; ++k) total += b[k];
+    }
+#pragma unroll
+    for (int j = 0; j < kPer; ++j) buf[(c + 1) & 1][j * 256 + threadIdx.x] = r[j];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = total;
 }
 
 // FAST: float64 accumulation in parallel, rounded once
@@ -205,7 +243,7 @@ extern "C" int tcs_edge_weights_ex(tcs_graph* g, const tcs_term* terms, int nter
       const float* d = raw.p + (size_t)ts.slot[t] * E;
       if (ts.norm[t] == TCS_NORM_GLOBAL) {
         if (mode == TCS_MODE_PARITY) {
-          LAUNCH(ctx, k_sum_sequential, 1, 32, 0, d, E, s32.p);
+          LAUNCH(ctx, k_sum_sequential, 1, 256, 0, d, E, s32.p);
         } else {
           CK(cudaMemsetAsync(s64.p, 0, 8, ctx->stream));
           LAUNCH(ctx, k_sum_f64, std::min<unsigned>(div_up(E, 256), ctx->sm_count * 4), 256, 0, d, E, s64.p);
