@@ -79,7 +79,9 @@ __global__ void k_edge_raw(size_t E, const uint32_t* __restrict__ esrc, const ui
 // of float additions, whose floor is the FADD latency (~4 cycles per edge).  The chain must not wait for memory: all 256
 // threads stream the values into shared memory one chunk ahead (coalesced, double-buffered) and thread 0 adds the
 // current chunk from shared memory with 16-byte loads that do not depend on the sum.  (One warp loading 32 values per
-// step and adding them through shuffles spent 15 ns per edge waiting for its own global load.)
+// step and adding them through shuffles spent 15 ns per edge waiting for its own global load.)  What is left is the chain itself:
+// 289 k edges take 0.88 ms whether the adds are FADD or FFMA(v, 1, total) - four cycles each at the ~1.3 GHz a
+// single-CTA kernel gets right after an idle period.
 constexpr int kSumChunk = 4096;
 __global__ void __launch_bounds__(256) k_sum_sequential(const float* __restrict__ d, size_t E, float* __restrict__ out) {
   __shared__ __align__(16) float buf[2][kSumChunk];
