@@ -285,6 +285,8 @@ __global__ void __launch_bounds__(1024) k_dense_invert(int m, const double* __re
 // took 46 us for m = 126: four CTAs of dependent loads.)
 __global__ void __launch_bounds__(128) k_dense_apply(int m, int Q, const double* __restrict__ Einv, const float4* __restrict__ r,
                                                      float4* __restrict__ e) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   __shared__ double sm[128 * 4];
   const int a = blockIdx.x;
   const int parts = blockDim.x / Q;
@@ -315,6 +317,8 @@ __global__ void __launch_bounds__(256) k_restrict(int nc, int Q, const uint32_t*
                                                   const uint32_t* __restrict__ cidx, const float4* __restrict__ rf,
                                                   const float* __restrict__ winvd, float4* __restrict__ rc,
                                                   float4* __restrict__ xc) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (t >= (size_t)nc * Q) return;
   const int a = (int)(t / Q), q = (int)(t - (size_t)a * Q);
@@ -351,6 +355,8 @@ __global__ void __launch_bounds__(256, 6) k_level_spmm(int n, int Q, const uint3
                                                     const float* __restrict__ gdiag, const float* __restrict__ winvd,
                                                     const float4* __restrict__ X, const float4* __restrict__ RHS,
                                                     float4* __restrict__ OUT, double* __restrict__ dots) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -401,6 +407,8 @@ __global__ void __launch_bounds__(256, 6) k_level_spmm(int n, int Q, const uint3
 // x[i] += over * e[agg[i]]
 __global__ void __launch_bounds__(256) k_prolong(int n, int Q, float over, const uint32_t* __restrict__ agg,
                                                  const float4* __restrict__ e, float4* __restrict__ x) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   if (t >= (size_t)n * Q) return;
   const int i = (int)(t / Q), q = (int)(t - (size_t)i * Q);
@@ -413,6 +421,8 @@ __global__ void __launch_bounds__(256) k_prolong(int n, int Q, float over, const
 // dots[c] += a . b per column (float64): the coarse part of r.z when level 1 is the dense bottom
 __global__ void __launch_bounds__(256) k_dot(int n, int Q, const float4* __restrict__ a, const float4* __restrict__ b,
                                              double* __restrict__ dots) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -622,7 +632,7 @@ template <int SMOOTH, int DOT>
 inline void launch_level_spmm(tcs_ctx* ctx, const Level& C, int Q, const float4* X, const float4* RHS, float4* OUT,
                               double* dots) {
   const size_t dsm = (size_t)4 * Q * sizeof(double);
-  LAUNCH(ctx, (k_level_spmm<SMOOTH, DOT>), spmm_grid(ctx, C.A.n, Q), 256, dsm, C.A.n, Q, C.A.rowptr, C.A.col, C.A.val,
+  LAUNCH_PDL(ctx, C.A.n, (k_level_spmm<SMOOTH, DOT>), spmm_grid(ctx, C.A.n, Q), 256, dsm, C.A.n, Q, C.A.rowptr, C.A.col, C.A.val,
            C.gdiag.p, C.winvd.p, X, RHS, OUT, dots);
 }
 
@@ -637,7 +647,7 @@ inline int apply(tcs_ctx* ctx, Hierarchy& H, int Q, const float4* R4, double* rz
     Level& F = H.L[l - 1];
     const float4* src = l == 1 ? R4 : (const float4*)F.t.p;
     const bool bottom = l == last;
-    LAUNCH(ctx, k_restrict, div_up((size_t)C.A.n * Q, 256), 256, 0, C.A.n, Q, F.cptr.p, F.cidx.p, src, C.winvd.p,
+    LAUNCH_PDL(ctx, C.A.n, k_restrict, div_up((size_t)C.A.n * Q, 256), 256, 0, C.A.n, Q, F.cptr.p, F.cidx.p, src, C.winvd.p,
            (float4*)C.r.p, bottom && H.dense ? (float4*)nullptr : (float4*)C.x.p);
     if (bottom) break;
     launch_level_spmm<0, 0>(ctx, C, Q, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, nullptr);
@@ -646,19 +656,19 @@ inline int apply(tcs_ctx* ctx, Hierarchy& H, int Q, const float4* R4, double* rz
   {
     Level& B = H.L[last];
     if (H.dense) {
-      LAUNCH(ctx, k_dense_apply, (unsigned)H.m, 128, 0, H.m, Q, H.Einv.p, (const float4*)B.r.p, (float4*)B.t.p);
+      LAUNCH_PDL(ctx, H.m, k_dense_apply, (unsigned)H.m, 128, 0, H.m, Q, H.Einv.p, (const float4*)B.r.p, (float4*)B.t.p);
     } else {
       // no dense inverse (many collapsed components): the smoother is exact on rows without off-diagonal entries
       launch_level_spmm<1, 0>(ctx, B, Q, (const float4*)B.x.p, (const float4*)B.r.p, (float4*)B.t.p, nullptr);
     }
     if (last == 1)
-      LAUNCH(ctx, k_dot, std::min(spmm_grid(ctx, B.A.n, Q), 64u), 256, dsm, B.A.n, Q, (const float4*)B.r.p, (const float4*)B.t.p, rz_target);
+      LAUNCH_PDL(ctx, B.A.n, k_dot, std::min(spmm_grid(ctx, B.A.n, Q), 64u), 256, dsm, B.A.n, Q, (const float4*)B.r.p, (const float4*)B.t.p, rz_target);
   }
   // up
   for (int l = last - 1; l >= 1; --l) {
     Level& C = H.L[l];
     Level& N = H.L[l + 1];
-    LAUNCH(ctx, k_prolong, div_up((size_t)C.A.n * Q, 256), 256, 0, C.A.n, Q, H.over, C.agg.p, (const float4*)N.t.p, (float4*)C.x.p);
+    LAUNCH_PDL(ctx, C.A.n, k_prolong, div_up((size_t)C.A.n * Q, 256), 256, 0, C.A.n, Q, H.over, C.agg.p, (const float4*)N.t.p, (float4*)C.x.p);
     if (l == 1)
       launch_level_spmm<1, 1>(ctx, C, Q, (const float4*)C.x.p, (const float4*)C.r.p, (float4*)C.t.p, rz_target);
     else

@@ -1,6 +1,7 @@
 // tcs_b200/csrc/api.cu - context management, cloud upload, graph accessors of the C ABI (include/tcs_b200.h).
 #include <cub/cub.cuh>
 
+#include <cstdlib>
 #include "common.cuh"
 
 int tcs_fail(tcs_ctx* ctx, int code, const char* fmt, ...) {
@@ -47,6 +48,7 @@ extern "C" int tcs_ctx_create_on_stream(int device, void* cuda_stream, tcs_ctx**
     return TCS_ERR_CUDA;
   }
   for (int i = 0; i < 32; ++i) cudaEventCreate(&ctx->ev[i]);
+  if (const char* v = getenv("TCS_PDL")) ctx->pdl = atoi(v) != 0;
   *out = ctx;
   return TCS_OK;
 }

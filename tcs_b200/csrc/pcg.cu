@@ -76,6 +76,8 @@ __global__ void __launch_bounds__(256) k_spmm(int n, int Q, const uint32_t* __re
                                               const int* __restrict__ col, const float* __restrict__ val,
                                               const float* __restrict__ gdiag, const float4* __restrict__ P,
                                               float4* __restrict__ AP, double* __restrict__ pAp) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   extern __shared__ double sm[];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -178,6 +180,8 @@ __global__ void __launch_bounds__(256) k_pcg_update(int n, int Q, const float4* 
                                                     const int* __restrict__ frozen, const double* __restrict__ rz0,
                                                     double done_factor, const double* __restrict__ pr,
                                                     double* __restrict__ rr_next) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   // rr_next (may be NULL): ||r||^2 of the recurrence residual per column - what the host probes between two float64
   // true-residual checks when the multilevel preconditioner is on
   extern __shared__ double sm[];
@@ -297,6 +301,8 @@ __global__ void __launch_bounds__(256) k_pcg_dir(int n, int Q, const float4* __r
                                                  const double* __restrict__ rz0, double done_factor,
                                                  const double* __restrict__ pr, const uint32_t* __restrict__ agg,
                                                  const float4* __restrict__ yc, int restart, double* __restrict__ X64) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   // X64 != NULL: x is advanced in float64 directly (x += alpha p with float64 products) instead of through the float32
   // increment Xd - with tens of iterations per solve the increment IS the solution, and its float32 rounding is the
   // other source of the white noise that costs the second refinement stage its iterations
@@ -1030,7 +1036,7 @@ void launch_spmm(tcs_ctx* ctx, tcs_system& S, const float4* P4, float4* AP4, dou
   const int n = S.n, Q = S.Kp / 4;
   if (S.ring) {
     const SpmmRing& T = S.rg;
-    LAUNCH(ctx, k_spmm_ring, (unsigned)T.nctas, kRingThreads, (size_t)T.total, n, Q, T, S.ring_meta.p, S.ring_blob.p, S.far_rows.p,
+    LAUNCH_PDL(ctx, n, k_spmm_ring, (unsigned)T.nctas, kRingThreads, (size_t)T.total, n, Q, T, S.ring_meta.p, S.ring_blob.p, S.far_rows.p,
            S.ring_desc.p, S.ring_cta_ptr.p, P4, AP4, pAp, (long long*)nullptr);
   } else if (S.tiled) {
     const SpmmTile& T = S.tile;
@@ -1040,7 +1046,7 @@ void launch_spmm(tcs_ctx* ctx, tcs_system& S, const float4* P4, float4* AP4, dou
            S.gdiag.p, P4, AP4, pAp);
   } else {
     const PcgLaunch L = pcg_launch_shape(ctx, n, Q, false);
-    LAUNCH(ctx, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.gdiag.p, P4, AP4, pAp);
+    LAUNCH_PDL(ctx, n, k_spmm, L.grid, L.block, L.smem, n, Q, S.rowptr.p, S.col.p, S.val.p, S.gdiag.p, P4, AP4, pAp);
   }
 }
 
@@ -1389,10 +1395,10 @@ int tcs_impl_pcg_solve(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts
       launch_spmm(ctx, S, P4, AP4, d_pAp + s0 * Kp0);
       if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
       ++spmm_launches;
-      LAUNCH(ctx, k_pcg_update, L.grid_update, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
+      LAUNCH_PDL(ctx, n, k_pcg_update, L.grid_update, L.block, L.smem, n, Qw, AP4, R4, invd.p, d_rz + s0 * Kp0, d_pAp + s0 * Kp0,
              d_rz + s1 * Kp0, frozen.p, d_rz0, done_factor, pr, AH.on ? d_rr3 + s1 * Kp0 : (double*)nullptr);
       if (AH.on) TRY(amg::apply(ctx, AH, Qw, R4, d_rz + s1 * Kp0));
-      LAUNCH(ctx, k_pcg_dir, L.grid_dir, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
+      LAUNCH_PDL(ctx, n, k_pcg_dir, L.grid_dir, L.block, 0, n, Qw, R4, P4, (float4*)Xd.p, invd.p, d_rz + s0 * Kp0,
              d_pAp + s0 * Kp0, d_rz + s1 * Kp0, d_pAp + s1 * Kp0, d_rz + s2 * Kp0,
              AH.on ? d_rr3 + s2 * Kp0 : (double*)nullptr, frozen.p, d_rz0, done_factor, pr,
              AH.on ? amg::fine_agg(AH) : (const uint32_t*)nullptr, AH.on ? amg::result(AH) : (const float4*)nullptr,

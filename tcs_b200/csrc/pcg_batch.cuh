@@ -21,6 +21,8 @@ namespace batch {
 // out[s][c] += sum over the rows of scene s of a[row][c] * b[row][c]
 __global__ void __launch_bounds__(256) k_dot(int Q, int Kp, const int* __restrict__ row_begin, const float4* __restrict__ A,
                                              const float4* __restrict__ B, double* __restrict__ out) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   extern __shared__ double sm[];
   const int s = blockIdx.y, r0 = row_begin[s], r1 = row_begin[s + 1];
   const int rows_per_block = blockDim.x / Q;
@@ -39,6 +41,8 @@ __global__ void __launch_bounds__(256) k_dot(int Q, int Kp, const int* __restric
 __global__ void __launch_bounds__(256) k_dot_rz(int Q, int Kp, const int* __restrict__ row_begin, const float4* __restrict__ R,
                                                 const float* __restrict__ invd, const uint32_t* __restrict__ agg,
                                                 const float4* __restrict__ e, double* __restrict__ rz, double* __restrict__ rr) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   extern __shared__ double sm[];
   const int s = blockIdx.y, r0 = row_begin[s], r1 = row_begin[s + 1];
   const int rows_per_block = blockDim.x / Q;
@@ -64,6 +68,8 @@ __global__ void __launch_bounds__(256) k_dot_rz(int Q, int Kp, const int* __rest
 __global__ void k_alpha(int count, const double* __restrict__ rz, const double* __restrict__ pAp, const double* __restrict__ rz0,
                         const int* __restrict__ frozen, double done_factor, float* __restrict__ al, double* __restrict__ clear_a,
                         double* __restrict__ clear_b) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count) return;
   const double den = pAp[i], num = rz[i];
@@ -77,6 +83,8 @@ __global__ void k_alpha(int count, const double* __restrict__ rz, const double* 
 // beta[s][c] = rz_new / rz ; clears the p.Ap accumulator of the next iteration
 __global__ void k_beta(int count, const double* __restrict__ rz, const double* __restrict__ rz_new, const double* __restrict__ rz0,
                        const int* __restrict__ frozen, double done_factor, float* __restrict__ be, double* __restrict__ clear_a) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= count) return;
   const double den = rz[i], num = rz_new[i];
@@ -89,6 +97,8 @@ __global__ void k_beta(int count, const double* __restrict__ rz, const double* _
 // r -= alpha[s] Ap
 __global__ void __launch_bounds__(256) k_update(int Q, int Kp, const int* __restrict__ row_begin, const float* __restrict__ al,
                                                 const float4* __restrict__ AP, float4* __restrict__ R) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   const int s = blockIdx.y, r0 = row_begin[s], r1 = row_begin[s + 1];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -112,6 +122,8 @@ __global__ void __launch_bounds__(256) k_dir(int Q, int Kp, const int* __restric
                                              const float* __restrict__ be, const float4* __restrict__ R, float4* __restrict__ P,
                                              double* __restrict__ X, const float* __restrict__ invd,
                                              const uint32_t* __restrict__ agg, const float4* __restrict__ e) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   const int s = blockIdx.y, r0 = row_begin[s], r1 = row_begin[s + 1];
   const int rows_per_block = blockDim.x / Q;
   const int local = threadIdx.x / Q, q = threadIdx.x - local * Q;
@@ -248,15 +260,15 @@ int pcg_solve_batched(tcs_ctx* ctx, tcs_system& S, int K, const tcs_solver_opts&
     if (timed) CK(cudaEventRecord(evs[2 * samples], ctx->stream));
     launch_spmm(ctx, S, P4, AP4, d_dummy);
     if (timed) { CK(cudaEventRecord(evs[2 * samples + 1], ctx->stream)); ++samples; }
-    LAUNCH(ctx, batch::k_dot, grid, 256, dsm, Q, Kp, d_rb.p, (const float4*)P4, (const float4*)AP4, d_pAp);
-    LAUNCH(ctx, batch::k_alpha, div_up(count, 128), 128, 0, count, d_rz[c], d_pAp, d_rz0, frozen.p, done_factor, d_al,
+    LAUNCH_PDL(ctx, n, batch::k_dot, grid, 256, dsm, Q, Kp, d_rb.p, (const float4*)P4, (const float4*)AP4, d_pAp);
+    LAUNCH_PDL(ctx, count, batch::k_alpha, div_up(count, 128), 128, 0, count, d_rz[c], d_pAp, d_rz0, frozen.p, done_factor, d_al,
            d_rz[c ^ 1], d_rr);
-    LAUNCH(ctx, batch::k_update, grid, 256, 0, Q, Kp, d_rb.p, d_al, (const float4*)AP4, R4);
+    LAUNCH_PDL(ctx, n, batch::k_update, grid, 256, 0, Q, Kp, d_rb.p, d_al, (const float4*)AP4, R4);
     TRY(amg::apply(ctx, AH, Q, R4, d_dummy));
-    LAUNCH(ctx, batch::k_dot_rz, grid, 256, dsm, Q, Kp, d_rb.p, R4, invd.p, agg, e1, d_rz[c ^ 1], d_rr);
-    LAUNCH(ctx, batch::k_beta, div_up(count, 128), 128, 0, count, d_rz[c], d_rz[c ^ 1], d_rz0, frozen.p, done_factor, d_be,
+    LAUNCH_PDL(ctx, n, batch::k_dot_rz, grid, 256, dsm, Q, Kp, d_rb.p, R4, invd.p, agg, e1, d_rz[c ^ 1], d_rr);
+    LAUNCH_PDL(ctx, count, batch::k_beta, div_up(count, 128), 128, 0, count, d_rz[c], d_rz[c ^ 1], d_rz0, frozen.p, done_factor, d_be,
            d_pAp);
-    LAUNCH(ctx, batch::k_dir, grid, 256, 0, Q, Kp, d_rb.p, d_al, d_be, R4, P4, X.p, invd.p, agg, e1);
+    LAUNCH_PDL(ctx, n, batch::k_dir, grid, 256, 0, Q, Kp, d_rb.p, d_al, d_be, R4, P4, X.p, invd.p, agg, e1);
     return TCS_OK;
   };
   struct ChunkGraph {

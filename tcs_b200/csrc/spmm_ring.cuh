@@ -188,6 +188,8 @@ __global__ void __launch_bounds__(kRingThreads, 1)
                 const int* __restrict__ far_rows, const uint4* __restrict__ desc, const int* __restrict__ cta_ptr,
                 const float4* __restrict__ P, float4* __restrict__ AP, double* __restrict__ pAp,
                 long long* __restrict__ cta_clk) {
+  pdl_wait();      // programmatic dependent launch: the kernel before this one has completed
+  pdl_trigger();   // ... and the one after it may be scheduled
   extern __shared__ __align__(128) unsigned char smem[];
   const long long clk0 = clock64();
   uint64_t* full = (uint64_t*)(smem + T.off_bar);
