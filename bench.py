@@ -107,6 +107,7 @@ class ClockSampler(threading.Thread):
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.rows, self._halt, self._armed = index, [], threading.Event(), threading.Event()
+        self.call_ms = []
         self.nv, self.h, self.source = None, None, "nvidia-smi"
         try:
             import pynvml
@@ -121,6 +122,8 @@ class ClockSampler(threading.Thread):
                 self.h = pynvml.nvmlDeviceGetHandleByIndex(int(ids[index]) if ids and ids[index].strip().isdigit() else index)
             self.nv, self.source = pynvml, "nvml"
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            for _ in range(3):          # the first call of an NVML query initialises state in the driver (tens of ms, and it
+                self._sample_nvml()     # stalls the GPU work of this process): pay that here, not inside the timed region
         except Exception:
             self.nv = None
 
@@ -148,7 +151,9 @@ class ClockSampler(threading.Thread):
                 continue
             try:
                 if self.nv is not None:
+                    t0 = time.perf_counter()
                     self.rows.append(self._sample_nvml())
+                    self.call_ms.append(1e3 * (time.perf_counter() - t0))
                 else:
                     out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
@@ -173,7 +178,8 @@ class ClockSampler(threading.Thread):
             except Exception:
                 continue
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_min_mhz": min(sm) if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm), "source": self.source + ", sampled inside the timed region only"}
+                "reasons": sorted(reasons), "samples": len(sm), "source": self.source + ", sampled inside the timed region only",
+                "query_ms_max": max(self.call_ms) if self.call_ms else None}
 
 
 def peaks():

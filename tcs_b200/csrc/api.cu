@@ -49,6 +49,7 @@ extern "C" int tcs_ctx_create_on_stream(int device, void* cuda_stream, tcs_ctx**
   }
   for (int i = 0; i < 32; ++i) cudaEventCreate(&ctx->ev[i]);
   if (const char* v = getenv("TCS_PDL")) ctx->pdl = atoi(v) != 0;
+  if (const char* v = getenv("TCS_PDL_ROWS")) ctx->pdl_rows = atoll(v);
   *out = ctx;
   return TCS_OK;
 }

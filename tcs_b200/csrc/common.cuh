@@ -35,6 +35,7 @@ struct tcs_ctx {
   size_t stage_cap = 0;
   cudaEvent_t ev[32];
   int pdl = 1;   // programmatic dependent launch for the kernels of a PCG iteration (TCS_PDL=0 switches it off)
+  long long pdl_rows = 65536;   // ... for launches of at most this many rows (TCS_PDL_ROWS)
 };
 
 int tcs_fail(tcs_ctx* ctx, int code, const char* fmt, ...);
@@ -220,10 +221,9 @@ __device__ __forceinline__ void f4_diff_fma(F4p& acc, float w, float4 v, const F
 // Measured (C4 scene / one 640x480 scene, solve time): every launch of the iteration programmatic 127.8 -> 132.7 ms /
 // 7.15 -> 5.65 ms - it pays where the kernels are launch-bound and costs where they are bandwidth-bound (dependents
 // scheduled early take SM resources from the kernel that still runs), hence the size limit.
-constexpr long long kPdlRows = 65536;
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
-// `rows`: size of the launch; only small kernels take the programmatic edge (kPdlRows)
+// `rows`: size of the launch; only small kernels take the programmatic edge (tcs_ctx::pdl_rows)
 #define LAUNCH_PDL(ctx, rows, kernel, grid, block, smem, ...)                                \
   do {                                                                                       \
     cudaLaunchConfig_t _cfg = {};                                                            \
@@ -231,7 +231,7 @@ __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.lau
     _cfg.dynamicSmemBytes = (size_t)(smem); _cfg.stream = (ctx)->stream;                     \
     cudaLaunchAttribute _at[1];                                                              \
     _at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                          \
-    _at[0].val.programmaticStreamSerializationAllowed = ((ctx)->pdl && (long long)(rows) <= kPdlRows) ? 1 : 0; \
+    _at[0].val.programmaticStreamSerializationAllowed = ((ctx)->pdl && (long long)(rows) <= (ctx)->pdl_rows) ? 1 : 0; \
     _cfg.attrs = _at; _cfg.numAttrs = 1;                                                     \
     cudaLaunchKernelEx(&_cfg, kernel, __VA_ARGS__);                                          \
     (ctx)->launches++;                                                                       \
