@@ -189,6 +189,48 @@ def test_fast_mode_default_solver_matches_oracle(ctx, case):
     g.close()
 
 
+def test_full_size_c4_labels_match_the_cpu_port(ctx):
+    """BASELINE.json configs[3] at FULL size (2.85 M vertices): the benchmarked path - FAST mode, default solver - against
+    the labels of the CPU oracle port for the same scene (fixture tests/golden/c4_scene0_cpu_labels.npz, generated by
+    tests/golden/make_c4_cpu_labels.py: 20-25 minutes per solve on one core).  The gate is north_star's: a vertex may
+    differ from the float64 direct solve only where that solve's top-2 potential gap is below 1e-6.  The fixture also
+    holds the labels of the float32 LDL^T (the reference's arithmetic): it differs from the float64 solve at 309
+    vertices with gaps up to 0.15 - wherever the GPU differs from the float32 labels, it must be because the float32
+    factorisation is off, i.e. the GPU agrees with float64 there."""
+    import json
+    import os
+    import bench
+    fix = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "c4_scene0_cpu_labels.npz"))
+
+    class A:
+        small = False
+    w, h, xyz, rgba, label, sx, sl = bench.c4_scene(A, 0)
+    ctx.upload_cloud(xyz, rgba)
+    r = ctx.segment_cloud(bench.C4_RES, sx, sl, preset=capi.PRESET_CLASS, mode=capi.MODE_FAST)
+    info = r["info"].as_dict()
+    assert r["status"] == capi.OK and info["converged"] and max(info["rel_residual"]) <= 1e-6
+    g = r["graph"]
+    assert (g.V, g.E) == (int(fix["V"]), int(fix["E"]))
+    got = r["vertex_colour"]
+    f64, f32 = fix["labels_f64"].astype(np.uint32), fix["labels_f32"].astype(np.uint32)
+    gap = np.full(g.V, np.inf, np.float32)          # float64 top-2 gaps below 1e-3; everything else is "far from a tie"
+    gap[fix["tie_idx"]] = fix["tie_gap"]
+    diff = np.nonzero(got != f64)[0]
+    d32 = np.nonzero(got != f32)[0]
+    rec = dict(tag="C4 full size FAST vs CPU port float64 LDL^T", V=int(g.V), mismatches=int(len(diff)),
+               max_gap=float(gap[diff].max()) if len(diff) else 0.0, vertices=[int(v) for v in diff[:32]],
+               gaps=[float(x) for x in gap[diff][:32]], bound=label_gate.NEAR_TIE_GAP, iterations=info["iterations"],
+               max_rel_residual=max(info["rel_residual"]), differs_from_float32_ldlt=int(len(d32)),
+               float32_ldlt_differs_from_float64=int(np.count_nonzero(f32 != f64)))
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    if os.path.isdir(out):
+        with open(os.path.join(out, "label_parity.jsonl"), "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    assert len(diff) == 0 or float(gap[diff].max()) < label_gate.NEAR_TIE_GAP, rec
+    assert np.all(f32[d32] != f64[d32]) or np.all(gap[d32[f32[d32] == f64[d32]]] < label_gate.NEAR_TIE_GAP), rec
+    g.close()
+
+
 def test_potentials_match_direct_solve(ctx, scenes):
     """Potentials of the PCG solve vs the oracle's float64 LDL^T on the same graph and weights."""
     sc = scenes["test1"]
