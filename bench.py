@@ -8,10 +8,12 @@ achieved HBM GB/s against the measured B200 peak in `roofline`.
   5 mm voxels (~2.85 M vertices, ~19.6 M edges), 16 labels x 10 seeds, class weight preset, FAST arithmetic mode,
   multilevel-preconditioned PCG to a float64 relative residual of 1e-6 per label column.  One step = one whole
   segmentation of one scene.  At N > 1 every rank segments its own scene (independent scenes are the path's natural
-  shard; no data-path collective) => weak scaling.  The S = min(N, 4) distinct scenes ROTATE over ranks and steps (rank r
-  runs scene (r + step) mod S), so with steps a multiple of S every rank does the same total work.
+  shard; no data-path collective) => weak scaling.  The same S = 2 scenes ROTATE over ranks and steps at every N,
+  N = 1 included (rank r runs scene (r + step) mod S), so with an even number of steps every rank of every N does the
+  same total work and the per-N values are comparable.
 --config c5 (BASELINE.json configs[4]): 1024 synthetic 640x480 scenes (~47 k vertices, 8 labels x 5 seeds each, 6 mm
-  voxels) round-robin over the ranks, segmented in batches through tcs_segment_batch (block-diagonal joint solve).
+  voxels) round-robin over the ranks, segmented in batches through tcs_segment_batch (block-diagonal joint solve) from three
+  worker contexts per GPU.
   One step = the whole job (1024 scenes); value = vertices/s (scenes/s in config).
 
   value : clouds already resident in HBM -> labels resident in HBM (CUDA events on the library's stream)
@@ -558,9 +560,7 @@ def run_c5(args, rank, local_rank, world):
     seeds = {k: (np.ascontiguousarray(data[k][2], np.float32), np.ascontiguousarray(data[k][3], np.uint32)) for k in distinct}
     # batches of at most --batch scenes, sized so that every worker context gets the same number of batches (128 scenes
     # on 3 contexts: 6 batches of 21-22 instead of 4 of 32, which would leave two contexts idle in the second round)
-    B = max(1, args.batch)
-    rounds = max(1, -(-len(mine) // (W * B)))
-    B = max(1, min(B, -(-len(mine) // (W * rounds))))
+    B = shard.balanced_batch(len(mine), W, max(1, args.batch))
     pc_host = [torch.empty((B, n), dtype=torch.int32).pin_memory() for _ in range(W)]
     vc_host = [torch.empty((B, n), dtype=torch.int32).pin_memory() for _ in range(W)]
     opts = capi.default_opts(time_spmm=0)

@@ -16,6 +16,19 @@ def scenes_for_rank(n_scenes: int, rank: int, world: int) -> List[int]:
     return list(range(rank, n_scenes, world))
 
 
+def balanced_batch(n_scenes: int, workers: int, max_batch: int) -> int:
+    """Scenes per tcs_segment_batch call for `n_scenes` scenes of one GPU served by `workers` contexts: at most
+    `max_batch`, and sized so that every worker gets the same number of batches (128 scenes on 3 contexts: 6 batches
+    of 21-22 instead of 4 of 32, which would leave two contexts idle in the second round).  The C++ driver uses the
+    same rule (include/tcs/batch_segmenter.h)."""
+    if workers < 1 or max_batch < 1:
+        raise ValueError("bad workers/max_batch")
+    if n_scenes <= 0:
+        return 1
+    rounds = max(1, -(-n_scenes // (workers * max_batch)))
+    return max(1, min(max_batch, -(-n_scenes // (workers * rounds))))
+
+
 def combine(local_units: float, local_ms: float, world: int) -> Tuple[float, float]:
     """(sum of units over ranks, max of milliseconds over ranks) - uses torch.distributed when world > 1."""
     if world == 1:

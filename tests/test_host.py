@@ -205,3 +205,18 @@ def test_bench_reference_arm_prints_its_line():
     r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--small",
                         "--steps", "1", "--warmup", "0"], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_balanced_batches_give_every_worker_the_same_number_of_batches():
+    from tcs_b200 import shard
+    assert shard.balanced_batch(1024, 3, 32) == 32          # 11 rounds of 3 batches: 1024 / 33 -> 32
+    assert shard.balanced_batch(128, 3, 32) == 22           # 2 rounds: 6 batches of <= 22
+    assert shard.balanced_batch(5, 3, 32) == 2 and shard.balanced_batch(0, 3, 32) == 1
+    for n in (1, 7, 31, 96, 97, 128, 500, 1024):
+        for w in (1, 2, 3, 5):
+            for b in (1, 4, 32):
+                step = shard.balanced_batch(n, w, b)
+                nb = -(-n // step)
+                assert 1 <= step <= b and nb <= w * max(1, -(-n // (w * b))), (n, w, b, step)
+    with pytest.raises(ValueError):
+        shard.balanced_batch(10, 0, 32)
